@@ -1,0 +1,310 @@
+// airc_api.cu -- the C ABI of include/aircraft_b200.h over the kernels in airc_kernels.cuh.
+// Built for sm_100a only (see __graft_entry__.build / Makefile).
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/aircraft_b200.h"
+#include "airc_fuse.hpp"
+#include "airc_kernels.cuh"
+
+using namespace airc;
+
+struct AircHandle {
+  DevConst dc;
+  int device;
+  int sm_count;
+  // used only by the *_host entry points (those are not re-entrant per handle)
+  void* scratch = nullptr;
+  size_t scratch_bytes = 0;
+  cudaStream_t hstream = nullptr;
+};
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, const char* detail) {
+  snprintf(g_err, sizeof(g_err), fmt, detail ? detail : "");
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                        \
+  do {                                                                        \
+    cudaError_t e__ = (expr);                                                 \
+    if (e__ != cudaSuccess) return fail(AIRC_ECUDA, #expr ": %s", cudaGetErrorString(e__)); \
+  } while (0)
+
+static int check_launch() {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(AIRC_ECUDA, "kernel launch: %s", cudaGetErrorString(e));
+  return AIRC_OK;
+}
+
+// RAII device switch so that calls work whatever device is current in the caller's thread
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = true;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+    if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+  }
+  ~DeviceGuard() {
+    int cur;
+    if (prev >= 0 && cudaGetDevice(&cur) == cudaSuccess && cur != prev) cudaSetDevice(prev);
+  }
+};
+
+static VecView view(const float* base, long long n, int dim, int layout) {
+  return layout == AIRC_LAYOUT_SOA ? VecView{base, 1, n} : VecView{base, (long long)dim, 1};
+}
+static VecViewW viewW(float* base, long long n, int dim, int layout) {
+  return layout == AIRC_LAYOUT_SOA ? VecViewW{base, 1, n} : VecViewW{base, (long long)dim, 1};
+}
+
+extern "C" {
+
+int airc_version(void) { return 100; }
+
+const char* airc_build_info(void) {
+  return "aircraft_b200 0.1.0 sm_100a (" __DATE__ " " __TIME__ ") kernels: state_derivative,"
+         " state_update, rollout, linearize, argmin";
+}
+
+const char* airc_last_error(const AircHandle*) { return g_err; }
+
+int airc_create(const AircParams* params, const AircNNBlob* nn, int device, AircHandle** out) {
+  if (!params || !nn || !out) return fail(AIRC_EINVAL, "airc_create: NULL argument%s", "");
+  if (!(params->mass > 0.0) || !(params->reference_area > 0.0))
+    return fail(AIRC_EINVAL, "airc_create: mass and reference_area must be positive%s", "");
+  for (int i = 0; i < 5; ++i)
+    if (!(nn->input_std[i] != 0.0f)) return fail(AIRC_EINVAL, "airc_create: input_std has a zero%s", "");
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(AIRC_ENODEV, "airc_create: no CUDA device (%s)", cudaGetErrorString(e));
+  if (device < 0 || device >= count) return fail(AIRC_EINVAL, "airc_create: bad device index%s", "");
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return fail(AIRC_ENODEV, "airc_create: device is not sm_100 (%s); this library has no other code path", prop.name);
+  AircHandle* h = new (std::nothrow) AircHandle;
+  if (!h) return fail(AIRC_ENOMEM, "airc_create: out of host memory%s", "");
+  build_devconst(*params, *nn, h->dc);
+  h->device = device;
+  h->sm_count = prop.multiProcessorCount;
+  *out = h;
+  return AIRC_OK;
+}
+
+int airc_destroy(AircHandle* h) {
+  if (!h) return AIRC_OK;
+  {
+    DeviceGuard g(h->device);
+    if (h->scratch) cudaFree(h->scratch);
+    if (h->hstream) cudaStreamDestroy(h->hstream);
+  }
+  delete h;
+  return AIRC_OK;
+}
+
+int airc_state_derivative(const AircHandle* h, const float* x, const float* u, int64_t n,
+                          int layout, float* xdot, void* stream) {
+  if (!h || !x || !u || !xdot || n < 0 || (layout != 0 && layout != 1))
+    return fail(AIRC_EINVAL, "airc_state_derivative: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(xdot, n, 13, layout), nullptr, 0.f, n, 1, 0};
+  const int bs = 128;
+  state_derivative_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  return check_launch();
+}
+
+int airc_state_update(const AircHandle* h, const float* x, const float* u, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                      int layout, float* x_next, void* stream) {
+  if (!h || !x || !u || !x_next || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
+      (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
+    return fail(AIRC_EINVAL, "airc_state_update: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(x_next, n, 13, layout),
+             dt_per_node, dt, n, substeps, (int)(flags & AIRC_FLAG_NORMALISE)};
+  const int bs = (n <= 148 * 64) ? 32 : 128;
+  state_update_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  return check_launch();
+}
+
+int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt, int64_t B,
+                 int H, int substeps, uint32_t flags, int layout, float* X, float* x_final,
+                 float* cost, const AircCostParams* cp, void* stream) {
+  if (!h || !x0 || (!U && H > 0) || B < 0 || H < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
+      (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U)) || (cost && !cp))
+    return fail(AIRC_EINVAL, "airc_rollout: bad argument%s", "");
+  if (B == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  RolloutArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x0 = view(x0, B, 13, layout);
+  a.U = U;
+  if (flags & AIRC_FLAG_SHARED_U) { a.u_sb = 0; a.u_sk = 7; a.u_sc = 1; }
+  else if (layout == AIRC_LAYOUT_SOA) { a.u_sb = 1; a.u_sk = 7 * B; a.u_sc = B; }
+  else { a.u_sb = 7LL * H; a.u_sk = 7; a.u_sc = 1; }
+  a.X = X;
+  if (layout == AIRC_LAYOUT_SOA) { a.X_sb = 1; a.X_sk = 13 * B; a.X_sc = B; }
+  else { a.X_sb = 13LL * (H + 1); a.X_sk = 13; a.X_sc = 1; }
+  a.xf = viewW(x_final, B, 13, layout);
+  a.cost = cost;
+  if (cost) {
+    a.cc = CostConst{cp->goal[0], cp->goal[1], cp->vel_param, cp->w_goal, cp->w_du,
+                     (float)(-1.4426950408889634 / (double)cp->du_eps), cp->w_height,
+                     H > 0 ? cp->w_speed / (float)H : 0.f, cp->w_vx, cp->w_vyz};
+  }
+  a.dt = dt; a.B = B; a.H = H; a.substeps = substeps;
+  a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+  // small batches: one warp per block so that every SM gets work
+  const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : 128);
+  const unsigned grid = (unsigned)((B + bs - 1) / bs);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cost && X) rollout_kernel<true, true><<<grid, bs, 0, st>>>(h->dc, a);
+  else if (cost) rollout_kernel<true, false><<<grid, bs, 0, st>>>(h->dc, a);
+  else if (X) rollout_kernel<false, true><<<grid, bs, 0, st>>>(h->dc, a);
+  else rollout_kernel<false, false><<<grid, bs, 0, st>>>(h->dc, a);
+  return check_launch();
+}
+
+int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt,
+                   const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                   float* x_next, float* A, float* Bm, void* stream) {
+  if (!h || !x || !u || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
+      (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
+    return fail(AIRC_EINVAL, "airc_linearize: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  LinArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x = view(x, n, 13, layout);
+  a.u = view(u, n, 7, layout);
+  a.xn = viewW(x_next, n, 13, layout);
+  a.A = A; a.Bm = Bm;
+  if (layout == AIRC_LAYOUT_SOA) { a.A_sn = 1; a.A_se = n; a.B_sn = 1; a.B_se = n; }
+  else { a.A_sn = 169; a.A_se = 1; a.B_sn = 91; a.B_se = 1; }
+  a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
+  a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+  const int bs = 128;
+  const long long threads = n * 16;
+  linearize_kernel<<<(unsigned)((threads + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  return check_launch();
+}
+
+int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
+                int64_t* out_idx, void* stream) {
+  if (!h || !cost || !out_idx || B <= 0 || B > 0xFFFFFFFFLL)
+    return fail(AIRC_EINVAL, "airc_argmin: bad argument%s", "");
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  // out_idx doubles as the 64-bit key during the reduction
+  CUDA_TRY(cudaMemsetAsync(out_idx, 0xFF, sizeof(int64_t), st));
+  long long blocks = (B + 255) / 256;
+  if (blocks > (long long)h->sm_count * 8) blocks = (long long)h->sm_count * 8;
+  argmin_kernel<<<(unsigned)blocks, 256, 0, st>>>(cost, B, (unsigned long long*)out_idx);
+  argmin_finish_kernel<<<1, 1, 0, st>>>((const unsigned long long*)out_idx, out_min, (long long*)out_idx);
+  return check_launch();
+}
+
+// ------------------------------------------------------------------ host-buffer entry points
+static int ensure_scratch(AircHandle* h, size_t bytes) {
+  if (!h->hstream) CUDA_TRY(cudaStreamCreateWithFlags(&h->hstream, cudaStreamNonBlocking));
+  if (bytes <= h->scratch_bytes) return AIRC_OK;
+  if (h->scratch) { cudaFree(h->scratch); h->scratch = nullptr; h->scratch_bytes = 0; }
+  size_t want = bytes + bytes / 4 + 4096;
+  cudaError_t e = cudaMalloc(&h->scratch, want);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(AIRC_ENOMEM, "cudaMalloc scratch: %s", cudaGetErrorString(e)); }
+  h->scratch_bytes = want;
+  return AIRC_OK;
+}
+
+static size_t al(size_t n_floats) { return ((n_floats * sizeof(float) + 255) / 256) * 256; }
+
+int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
+                           int substeps, uint32_t flags, int layout, float* x_next) {
+  if (!h || !x || !u || !x_next || n < 0) return fail(AIRC_EINVAL, "airc_state_update_host: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t bx = al(13 * n), bu = al(7 * n);
+  int rc = ensure_scratch(h, 2 * bx + bu);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float *dx = (float*)base, *du = (float*)(base + bx), *dn = (float*)(base + bx + bu);
+  CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_state_update(h, dx, du, dt, nullptr, n, substeps, flags, layout, dn, h->hstream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
+int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, int64_t B, int H,
+                      int substeps, uint32_t flags, int layout, float* X, float* x_final,
+                      float* cost, const AircCostParams* cp) {
+  if (!h || !x0 || (!U && H > 0) || B < 0 || H < 0) return fail(AIRC_EINVAL, "airc_rollout_host: bad argument%s", "");
+  if (B == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t nU = (flags & AIRC_FLAG_SHARED_U) ? (size_t)7 * H : (size_t)7 * H * B;
+  const size_t nX = X ? (size_t)13 * (H + 1) * B : 0;
+  const size_t bx = al(13 * B), bU = al(nU), bX = al(nX), bc = al(B);
+  int rc = ensure_scratch(h, 2 * bx + bU + bX + bc);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float* dx0 = (float*)base;
+  float* dU = (float*)(base + bx);
+  float* dX = X ? (float*)(base + bx + bU) : nullptr;
+  float* dxf = x_final ? (float*)(base + bx + bU + bX) : nullptr;
+  float* dc = cost ? (float*)(base + 2 * bx + bU + bX) : nullptr;
+  CUDA_TRY(cudaMemcpyAsync(dx0, x0, 13 * B * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  if (nU) CUDA_TRY(cudaMemcpyAsync(dU, U, nU * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_rollout(h, dx0, dU, dt, B, H, substeps, flags, layout, dX, dxf, dc, cp, h->hstream);
+  if (rc) return rc;
+  if (X) CUDA_TRY(cudaMemcpyAsync(X, dX, nX * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (x_final) CUDA_TRY(cudaMemcpyAsync(x_final, dxf, 13 * B * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (cost) CUDA_TRY(cudaMemcpyAsync(cost, dc, B * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
+int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
+                        int substeps, uint32_t flags, int layout, float* x_next, float* A,
+                        float* Bm) {
+  if (!h || !x || !u || n < 0) return fail(AIRC_EINVAL, "airc_linearize_host: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t bx = al(13 * n), bu = al(7 * n), bA = A ? al(169 * n) : 0, bB = Bm ? al(91 * n) : 0;
+  int rc = ensure_scratch(h, 2 * bx + bu + bA + bB);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float* dx = (float*)base;
+  float* du = (float*)(base + bx);
+  float* dn = x_next ? (float*)(base + bx + bu) : nullptr;
+  float* dA = A ? (float*)(base + 2 * bx + bu) : nullptr;
+  float* dB = Bm ? (float*)(base + 2 * bx + bu + bA) : nullptr;
+  CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_linearize(h, dx, du, dt, nullptr, n, substeps, flags, layout, dn, dA, dB, h->hstream);
+  if (rc) return rc;
+  if (x_next) CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (A) CUDA_TRY(cudaMemcpyAsync(A, dA, 169 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (Bm) CUDA_TRY(cudaMemcpyAsync(Bm, dB, 91 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
+}  // extern "C"

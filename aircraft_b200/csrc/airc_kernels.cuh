@@ -1,0 +1,333 @@
+// airc_kernels.cuh -- sm_100a kernels of the aircraft hot path.
+//
+//   K0  state_derivative_kernel   f(x,u) at n nodes                       (base.py:385-406)
+//   K0' state_update_kernel       Phi(x,u,dt) at n nodes                  (base.py:450-480)
+//   K1  rollout_kernel            B trajectories x H steps, state in registers for the whole
+//                                 horizon, optional trajectory write-out and fused cost (K3)
+//   K2  linearize_kernel          (x+, dPhi/dx, dPhi/du) at n nodes, forward mode,
+//                                 one tangent column per lane (16 lanes per node)
+//   K3' argmin_kernel             (min, argmin) over costs, warp shuffles + 64-bit atomicMin
+//
+// All global accesses go through explicit element strides so that the same kernels serve the
+// native SoA layout (batch index fastest => every warp access is one coalesced 128-byte line)
+// and the AoS convenience layout.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "airc_step.cuh"
+
+namespace airc {
+
+struct VecView {      // a batched small vector: element (b, c) at base[b*sb + c*sc]
+  const float* base;
+  long long sb, sc;
+};
+struct VecViewW {
+  float* base;
+  long long sb, sc;
+};
+
+AIRC_D void load_state(const VecView& X, long long b, State& s) {
+  const float* p = X.base + b * X.sb;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    s.p[i] = __ldg(p + i * X.sc);
+    s.v[i] = __ldg(p + (3 + i) * X.sc);
+    s.w[i] = __ldg(p + (10 + i) * X.sc);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) s.q[i] = __ldg(p + (6 + i) * X.sc);
+}
+
+AIRC_D void store_state(const VecViewW& X, long long b, const State& s) {
+  float* p = X.base + b * X.sb;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    p[i * X.sc] = s.p[i];
+    p[(3 + i) * X.sc] = s.v[i];
+    p[(10 + i) * X.sc] = s.w[i];
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) p[(6 + i) * X.sc] = s.q[i];
+}
+
+AIRC_D Ctl load_ctl(const float* u, long long sc) {
+  Ctl c;
+  c.da = __ldg(u);
+  c.de = __ldg(u + sc);
+  c.dr = __ldg(u + 2 * sc);
+  c.df = __ldg(u + 6 * sc);
+  return c;
+}
+
+// ------------------------------------------------------------------------------------ K0
+struct NodeArgs {
+  VecView x, u;
+  VecViewW out;
+  const float* dt_per_node;
+  float dt;
+  long long n;
+  int substeps;
+  int normalise;
+};
+
+__global__ void __launch_bounds__(128)
+state_derivative_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  State s;
+  load_state(a.x, i, s);
+  const Ctl c = load_ctl(a.u.base + i * a.u.sb, a.u.sc);
+  State d;
+  Stage st;
+  float J[6][5];
+  f_eval<false>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) d.p[k] = s.v[k];
+  store_state(a.out, i, d);
+}
+
+__global__ void __launch_bounds__(128)
+state_update_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  State s;
+  load_state(a.x, i, s);
+  const Ctl c = load_ctl(a.u.base + i * a.u.sb, a.u.sc);
+  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + i) : a.dt;
+  state_update<0>(P, s, c, dt, a.substeps, a.normalise != 0, nullptr);
+  store_state(a.out, i, s);
+}
+
+// ------------------------------------------------------------------------------------ K1
+struct CostConst {
+  float goal0, goal1, vel_param, w_goal, w_du, neg_log2e_over_eps, w_height, w_speed_over_H,
+      w_vx, w_vyz;
+};
+
+struct RolloutArgs {
+  VecView x0;
+  const float* U;            // element (b,k,c) at U[b*u_sb + k*u_sk + c*u_sc]
+  long long u_sb, u_sk, u_sc;
+  float* X;                  // optional trajectory, element (b,k,c) at X[b*X_sb + k*X_sk + c*X_sc]
+  long long X_sb, X_sk, X_sc;
+  VecViewW xf;               // optional final state
+  float* cost;               // optional
+  CostConst cc;
+  float dt;
+  long long B;
+  int H;
+  int substeps;
+  int normalise;
+};
+
+// |v_b|^2 of the node, for the speed term of the loss (control.py:63-64 evaluates
+// aircraft.v_frd_rel on every node of the trajectory).
+AIRC_D float body_speed2(const DevConst& P, const State& s) {
+  float M[9], n2;
+  rot_matrix(s.q, M, n2);
+  const float inv = rcp_nr(n2);
+  float acc = 0.0f;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float a = M[i] * s.v[0];
+    a = fmaf(M[3 + i], s.v[1], a);
+    a = fmaf(M[6 + i], s.v[2], a);
+    a = fmaf(a, inv, P.eps);
+    acc = fmaf(a, a, acc);
+  }
+  return acc;
+}
+
+template <bool COST, bool TRAJ>
+__global__ void __launch_bounds__(128)
+rollout_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= a.B) return;
+  State s;
+  load_state(a.x0, b, s);
+  const float z0 = s.p[2];
+  const float* u = a.U + b * a.u_sb;
+  float* Xb = TRAJ ? a.X + b * a.X_sb : nullptr;
+  const VecViewW Xv{Xb, 0, a.X_sc};
+  if (TRAJ) store_state(Xv, 0, s);
+
+  float sum_du = 0.0f, sum_v2 = 0.0f;
+  float up[7];
+#pragma unroll 1
+  for (int k = 0; k < a.H; ++k) {
+    const float* uk = u + k * a.u_sk;
+    const Ctl c = load_ctl(uk, a.u_sc);
+    if (COST) {
+      // smooth-L0 penalty on control increments, all 7 rows (control.py:22-23,47-48)
+      float un[7];
+      un[0] = c.da; un[1] = c.de; un[2] = c.dr; un[6] = c.df;
+#pragma unroll
+      for (int i = 3; i < 6; ++i) un[i] = __ldg(uk + i * a.u_sc);
+      if (k > 0) {
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const float d = un[i] - up[i];
+          sum_du += 1.0f - fast_ex2(d * d * a.cc.neg_log2e_over_eps);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 7; ++i) up[i] = un[i];
+      sum_v2 += body_speed2(P, s);
+    }
+    state_update<0>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
+    if (TRAJ) {
+      const VecViewW Xk{Xb + (long long)(k + 1) * a.X_sk, 0, a.X_sc};
+      store_state(Xk, 0, s);
+    }
+  }
+  if (a.xf.base) store_state(a.xf, b, s);
+  if (COST) {
+    const float ex = s.p[0] - a.cc.goal0, ey = s.p[1] - a.cc.goal1, ez = s.p[2] - z0;
+    float J = a.cc.w_goal * (ex * ex + ey * ey);
+    J = fmaf(a.cc.w_du, sum_du, J);
+    J = fmaf(a.cc.w_height, ez * ez, J);
+    J = fmaf(-a.cc.w_speed_over_H, sum_v2, J);
+    J = fmaf(a.cc.vel_param * a.cc.w_vx, s.v[0], J);
+    J = fmaf(a.cc.w_vyz, s.v[1] * s.v[1] + s.v[2] * s.v[2], J);
+    a.cost[b] = J;
+  }
+}
+
+// ------------------------------------------------------------------------------------ K2
+struct LinArgs {
+  VecView x, u;
+  VecViewW xn;               // optional
+  float* A;                  // optional; element (node, r, c) at A[node*A_sn + (r*13+c)*A_se]
+  long long A_sn, A_se;
+  float* Bm;                 // optional; element (node, r, c) at Bm[node*B_sn + (r*7+c)*B_se]
+  long long B_sn, B_se;
+  const float* dt_per_node;
+  float dt;
+  long long n;
+  int substeps;
+  int normalise;
+};
+
+// 16 lanes per node.  Lanes 0..9 carry the tangent columns of the state components the
+// dynamics depend on (v, q, omega = state indices 3..12), lanes 10..13 the four live control
+// columns (aileron, elevator, rudder, flaps = control indices 0,1,2,6).  f does not read p and
+// thrust is inert (aircraft.py:320), so dPhi/dp = [I;0] and dPhi/du[:,3:6] = 0 exactly: lanes
+// 14 and 15 write those constant columns.  Each lane pushes its column through the four RK4
+// stages (and all substeps) next to the primal, so nothing is exchanged between lanes.
+__global__ void __launch_bounds__(128)
+linearize_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long node = gt >> 4;
+  const int lane = (int)(gt & 15);
+  if (node >= a.n) return;
+  State s;
+  load_state(a.x, node, s);
+  const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
+  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
+
+  Tangent T;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    T.p[i] = 0.0f;
+    T.v[i] = (lane == i) ? 1.0f : 0.0f;
+    T.w[i] = (lane == 7 + i) ? 1.0f : 0.0f;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) T.q[i] = (lane == 3 + i) ? 1.0f : 0.0f;
+  T.dc.da = (lane == 10) ? 1.0f : 0.0f;
+  T.dc.de = (lane == 11) ? 1.0f : 0.0f;
+  T.dc.dr = (lane == 12) ? 1.0f : 0.0f;
+  T.dc.df = (lane == 13) ? 1.0f : 0.0f;
+
+  state_update<1>(P, s, c, dt, a.substeps, a.normalise != 0, &T);
+
+  if (lane == 0 && a.xn.base) store_state(a.xn, node, s);
+
+  float col[13];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { col[i] = T.p[i]; col[3 + i] = T.v[i]; col[10 + i] = T.w[i]; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) col[6 + i] = T.q[i];
+
+  if (lane < 10) {
+    if (a.A) {
+      float* o = a.A + node * a.A_sn + (long long)(3 + lane) * a.A_se;
+#pragma unroll
+      for (int r = 0; r < 13; ++r) o[(long long)(r * 13) * a.A_se] = col[r];
+    }
+  } else if (lane < 14) {
+    if (a.Bm) {
+      const int cu = (lane == 13) ? 6 : lane - 10;
+      float* o = a.Bm + node * a.B_sn + (long long)cu * a.B_se;
+#pragma unroll
+      for (int r = 0; r < 13; ++r) o[(long long)(r * 7) * a.B_se] = col[r];
+    }
+  } else if (lane == 14) {
+    if (a.A) {
+      float* o = a.A + node * a.A_sn;
+#pragma unroll
+      for (int r = 0; r < 13; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) o[(long long)(r * 13 + cc) * a.A_se] = (r == cc) ? 1.0f : 0.0f;
+    }
+  } else {
+    if (a.Bm) {
+      float* o = a.Bm + node * a.B_sn;
+#pragma unroll
+      for (int r = 0; r < 13; ++r)
+#pragma unroll
+        for (int cc = 3; cc < 6; ++cc) o[(long long)(r * 7 + cc) * a.B_se] = 0.0f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ K3'
+// Order-independent (min, argmin): key = (orderable bits of cost) << 32 | index-in-chunk.
+// The 64-bit minimum is exact and ties resolve to the lower index; NaN costs sort last.
+AIRC_D unsigned int float_orderable(float f) {
+  unsigned int u = __float_as_uint(f);
+  if (f != f) return 0xFFFFFFFFu;
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+AIRC_D float orderable_float(unsigned int k) {
+  const unsigned int u = (k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k;
+  return __uint_as_float(u);
+}
+
+__global__ void __launch_bounds__(256)
+argmin_kernel(const float* __restrict__ cost, long long B, unsigned long long* __restrict__ key) {
+  unsigned long long best = 0xFFFFFFFFFFFFFFFFull;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B;
+       i += (long long)gridDim.x * blockDim.x) {
+    const unsigned long long k =
+        ((unsigned long long)float_orderable(__ldg(cost + i)) << 32) | (unsigned long long)(unsigned int)i;
+    best = k < best ? k : best;
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, best, off);
+    best = o < best ? o : best;
+  }
+  __shared__ unsigned long long sm[8];
+  const int wid = threadIdx.x >> 5, ln = threadIdx.x & 31;
+  if (ln == 0) sm[wid] = best;
+  __syncthreads();
+  if (wid == 0) {
+    best = (ln < (int)(blockDim.x >> 5)) ? sm[ln] : 0xFFFFFFFFFFFFFFFFull;
+#pragma unroll
+    for (int off = 4; off > 0; off >>= 1) {
+      const unsigned long long o = __shfl_xor_sync(0xFFFFFFFFu, best, off);
+      best = o < best ? o : best;
+    }
+    if (ln == 0) atomicMin(key, best);
+  }
+}
+
+__global__ void argmin_finish_kernel(const unsigned long long* key, float* out_min, long long* out_idx) {
+  const unsigned long long k = *key;
+  if (out_min) *out_min = orderable_float((unsigned int)(k >> 32));
+  if (out_idx) *out_idx = (long long)(k & 0xFFFFFFFFull);
+}
+
+}  // namespace airc

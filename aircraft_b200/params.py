@@ -1,0 +1,83 @@
+"""Packs the reference's artefacts into the two C-ABI structs.
+
+  checkpoint  data/networks/model-dynamics.pth, read exactly as the reference's loader does
+              (/root/reference/src/aircraft/utils.py:30-40: torch.load(weights_only=True),
+              keys model_state_dict + input/output mean/std)      -> AircNNBlob (verbatim FP32)
+  constants   AircraftConfiguration + SixDOFOpts                   -> AircParams (float64)
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+from typing import Sequence
+
+import numpy as np
+import torch
+
+from ._cabi import AircNNBlob, AircParams, AircCostParams
+from .config import AircraftConfiguration, DEFAULT_MODEL_PATH, inertia_about_com
+
+_BLOB_FIELDS = [
+    ("W1", "core_layers.0.weight", (16, 5)), ("b1", "core_layers.0.bias", (16,)),
+    ("W2", "core_layers.1.weight", (32, 16)), ("b2", "core_layers.1.bias", (32,)),
+    ("W3", "core_layers.3.weight", (6, 32)), ("b3", "core_layers.3.bias", (6,)),
+]
+_SCALER_FIELDS = [("input_mean", 5), ("input_std", 5), ("output_mean", 6), ("output_std", 6)]
+
+
+def load_nn_blob(path: Path | str = DEFAULT_MODEL_PATH) -> AircNNBlob:
+    path = Path(path) if path else DEFAULT_MODEL_PATH
+    ck = torch.load(str(path), map_location="cpu", weights_only=True)
+    sd = ck["model_state_dict"]
+    blob = AircNNBlob()
+    for fld, key, shape in _BLOB_FIELDS:
+        t = sd[key].detach().to(torch.float32).contiguous()
+        if tuple(t.shape) != shape:
+            raise RuntimeError(f"{path}: {key} has shape {tuple(t.shape)}, expected {shape} "
+                               "(ScaledModel 5->16->32->tanh->6)")
+        arr = getattr(blob, fld)
+        arr[:] = t.reshape(-1).tolist()
+    for fld, n in _SCALER_FIELDS:
+        t = ck[fld].detach().to(torch.float32).reshape(-1)
+        if t.numel() != n:
+            raise RuntimeError(f"{path}: {fld} has {t.numel()} entries, expected {n}")
+        getattr(blob, fld)[:] = t.tolist()
+    return blob
+
+
+def nn_blob_from_arrays(W1, b1, W2, b2, W3, b3, in_mean, in_std, out_mean, out_std) -> AircNNBlob:
+    """For tests: a blob from arbitrary weights of the same architecture."""
+    blob = AircNNBlob()
+    for fld, val in zip(["W1", "b1", "W2", "b2", "W3", "b3", "input_mean", "input_std",
+                         "output_mean", "output_std"],
+                        [W1, b1, W2, b2, W3, b3, in_mean, in_std, out_mean, out_std]):
+        a = np.ascontiguousarray(np.asarray(val, np.float32)).reshape(-1)
+        getattr(blob, fld)[:] = a.tolist()
+    return blob
+
+
+def make_params(cfg: AircraftConfiguration, com: Sequence[float] | None = None,
+                gravity: Sequence[float] = (0.0, 0.0, 9.81), epsilon: float = 1e-6,
+                stall_scaling: bool = False) -> AircParams:
+    com = list(cfg.aero_centre_offset if com is None else com)
+    inertia, inv = inertia_about_com(cfg, com)
+    p = AircParams()
+    p.mass, p.span, p.chord = float(cfg.mass), float(cfg.span), float(cfg.chord)
+    p.reference_area = float(cfg.reference_area)
+    p.com[:] = [float(c) for c in com]
+    p.inertia[:] = inertia.reshape(-1).tolist()
+    p.inertia_inv[:] = inv.reshape(-1).tolist()
+    p.gravity[:] = [float(g) for g in gravity]
+    p.epsilon = float(epsilon)
+    p.stall_scaling = int(bool(stall_scaling))
+    return p
+
+
+def make_cost_params(goal=(150.0, 0.0), vel_param=1.0, w_goal=1000.0, w_du=100.0, du_eps=1e-2,
+                     w_height=1.0, w_speed=0.01, w_vx=1000.0, w_vyz=1000.0) -> AircCostParams:
+    """Weights of the primary MPC loss, /root/reference/main/control/control.py:35-70."""
+    c = AircCostParams()
+    c.goal[:] = [float(goal[0]), float(goal[1])]
+    c.vel_param, c.w_goal, c.w_du, c.du_eps = float(vel_param), float(w_goal), float(w_du), float(du_eps)
+    c.w_height, c.w_speed, c.w_vx, c.w_vyz = float(w_height), float(w_speed), float(w_vx), float(w_vyz)
+    return c

@@ -1,0 +1,168 @@
+/* aircraft_b200.h -- C ABI of the B200-native AIrcraft hot path.
+ *
+ * One shared library (libaircraft_b200.so), plain pointers and sizes, no torch types.
+ * It replaces, for numeric evaluation, the CasADi Functions the reference builds in
+ *   /root/reference/src/aircraft/dynamics/base.py:385-406   state_derivative  f(x,u)
+ *   /root/reference/src/aircraft/dynamics/base.py:408-446   state_step        (RK4)
+ *   /root/reference/src/aircraft/dynamics/base.py:450-480   state_update      Phi(x,u,dt)
+ * with the NN coefficient model of
+ *   /root/reference/src/aircraft/dynamics/coefficient_models.py:91-104 (NeuralModel)
+ *   /root/reference/src/aircraft/surrogates/models.py:101-155          (ScaledModel)
+ * and the derivative evaluations the reference obtains from ca.jacobian
+ *   /root/reference/src/aircraft/control/aircraft.py:85-95, base.py:51-52,
+ *   /root/reference/main/stability/stability.py:48-54.
+ *
+ * State  x[13] = [p_ned(3), v_ned(3), q_frd_ned xyzw(4), omega_frd(3)]   (base.py:94-99)
+ * Control u[7] = [aileron, elevator, rudder, thrust(3), flaps]           (aircraft.py:152-158)
+ *
+ * All data pointers are CALLER-OWNED DEVICE buffers of FP32 unless a function name ends in
+ * _host.  Kernels are enqueued on `stream` (a cudaStream_t passed as void*; NULL = legacy
+ * default stream) and the call returns without synchronising.  The handle owns only the
+ * constant block; it is immutable after create and may be used from several threads/streams.
+ * Every function returns 0 on success or a negative AIRC_E* code; none throws.
+ * NaN/Inf propagate through the arithmetic unchanged, as in the reference
+ * (main/dynamics/dynamics.py:108-110 checks them on the caller's side).
+ */
+#ifndef AIRCRAFT_B200_H
+#define AIRCRAFT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AIRC_NX 13
+#define AIRC_NU 7
+#define AIRC_NN_BLOB_FLOATS 860 /* see AircNNBlob below */
+
+/* error codes */
+#define AIRC_OK 0
+#define AIRC_EINVAL (-1)   /* bad argument (NULL, negative size, unknown flag/layout) */
+#define AIRC_ECUDA (-2)    /* CUDA runtime error; text via airc_last_error() */
+#define AIRC_ENODEV (-3)   /* no usable sm_100 device */
+#define AIRC_ENOMEM (-4)
+
+/* layout of batched vectors */
+#define AIRC_LAYOUT_SOA 0  /* [13][B] / [H][7][B]: batch index fastest -- the native layout; it is
+                              also the reference's numpy layout state[13,N], control[7,N]
+                              (main/control/control.py:77-90)                                   */
+#define AIRC_LAYOUT_AOS 1  /* [B][13] / [B][H][7] */
+
+/* flags */
+#define AIRC_FLAG_NORMALISE 1u   /* q <- q/|q| as base.py:443-444 / :473-474 (opts['quaternion']=='integration') */
+#define AIRC_FLAG_SHARED_U  2u   /* rollout: U is one [H][7] sequence shared by all trajectories */
+
+/* Aircraft constants: AircraftConfiguration (utils.py:201-215), SixDOFOpts (base.py:9-14),
+ * AircraftOpts (aircraft.py:22-38).  inertia / inertia_inv are about the shifted CoM
+ * (aircraft.py:168-187, base.py:139-144) and are computed by the host side in float64. */
+typedef struct AircParams {
+  double mass;
+  double span;
+  double chord;
+  double reference_area;
+  double com[3];          /* aero_centre_offset */
+  double inertia[9];      /* row-major 3x3 */
+  double inertia_inv[9];  /* row-major 3x3 */
+  double gravity[3];      /* NED, default {0,0,9.81} */
+  double epsilon;         /* default 1e-6 */
+  int32_t stall_scaling;  /* aircraft.py:280-294, default 0 */
+  int32_t reserved;
+} AircParams;
+
+/* The surrogate checkpoint, verbatim FP32 tensors of data/networks/model-dynamics.pth in this
+ * order (train_nn_surrogate.py:246-252): W1[16][5] b1[16] W2[32][16] b2[32] W3[6][32] b3[6]
+ * input_mean[5] input_std[5] output_mean[6] output_std[6]  = 860 floats.
+ * The library folds L1.L2 and the scalers in float64 at create time. */
+typedef struct AircNNBlob {
+  float W1[16 * 5];
+  float b1[16];
+  float W2[32 * 16];
+  float b2[32];
+  float W3[6 * 32];
+  float b3[6];
+  float input_mean[5];
+  float input_std[5];
+  float output_mean[6];
+  float output_std[6];
+} AircNNBlob;
+
+/* Primary MPC cost of main/control/control.py:35-70:
+ *  w_goal*|p_N[:2]-goal|^2 + w_du*sum_{k,i}(1-exp(-du^2/du_eps)) + w_height*(z_N-z_0)^2
+ *  - w_speed*sum_k |v_b(x_k)|^2/H + vel_param*w_vx*vx_N + w_vyz*(vy_N^2+vz_N^2)          */
+typedef struct AircCostParams {
+  float goal[2];
+  float vel_param;
+  float w_goal;    /* 1000 */
+  float w_du;      /* 100  */
+  float du_eps;    /* 1e-2 */
+  float w_height;  /* 1    */
+  float w_speed;   /* 1/100 */
+  float w_vx;      /* 1000 */
+  float w_vyz;     /* 1000 */
+} AircCostParams;
+
+typedef struct AircHandle AircHandle;
+
+/* version / introspection */
+int airc_version(void);
+const char* airc_build_info(void);
+
+/* Create a handle for CUDA device `device`.  `nn` may be a HOST pointer only. */
+int airc_create(const AircParams* params, const AircNNBlob* nn, int device, AircHandle** out);
+int airc_destroy(AircHandle* h);
+const char* airc_last_error(const AircHandle* h);
+
+/* f(x,u): replaces ca.Function 'dynamics' (base.py:402-406).  n nodes. */
+int airc_state_derivative(const AircHandle* h, const float* x, const float* u, int64_t n,
+                          int layout, float* xdot, void* stream);
+
+/* Phi(x,u,dt): replaces ca.Function 'state_update' (base.py:476-480) for n independent
+ * (x,u,dt) nodes.  dt_per_node may be NULL (then dt is used for all nodes). */
+int airc_state_update(const AircHandle* h, const float* x, const float* u, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                      int layout, float* x_next, void* stream);
+
+/* x[k+1] = Phi(x[k],u[k],dt), k<H, for B independent trajectories, each kept in registers for
+ * the whole horizon: replaces the Python loops of main/control/control.py:84-90,
+ * control/moving_horizon.py:208-213, main/dynamics/dynamics.py:105-121.
+ *   x0      [13][B] (SOA) or [B][13] (AOS)
+ *   U       [H][7][B] (SOA) / [B][H][7] (AOS) / [H][7] with AIRC_FLAG_SHARED_U
+ *   X       optional full trajectory [H+1][13][B] (SOA) / [B][H+1][13] (AOS), or NULL
+ *   x_final optional [13][B] / [B][13], or NULL
+ *   cost    optional [B] (needs cost_params), or NULL                                     */
+int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt, int64_t B,
+                 int H, int substeps, uint32_t flags, int layout, float* X, float* x_final,
+                 float* cost, const AircCostParams* cost_params, void* stream);
+
+/* (x+, A = dPhi/dx [13][13], Bm = dPhi/du [13][7]) at n nodes by forward-mode tangents:
+ * replaces ca.jacobian(state_update, x|u) (control/aircraft.py:88, base.py:51-52).
+ *   SOA: x[13][n] u[7][n] x_next[13][n] A[169][n] Bm[91][n]   (row-major 13x13 / 13x7 index first)
+ *   AOS: x[n][13] u[n][7] x_next[n][13] A[n][13][13] Bm[n][13][7]
+ * x_next, A, Bm may each be NULL.                                                          */
+int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt,
+                   const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                   float* x_next, float* A, float* Bm, void* stream);
+
+/* (min, argmin) of cost[B] by warp-shuffle + 64-bit atomicMin; ties go to the lower index.
+ * out_min: 1 float, out_idx: 1 int64 (device). */
+int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
+                int64_t* out_idx, void* stream);
+
+/* Convenience for FFI callers that hold HOST buffers (the cgo/ctypes style binding a maintainer
+ * of the reference would use from numpy): allocates device scratch, copies in, runs, copies out,
+ * synchronises.  Same semantics as the device-pointer versions. */
+int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
+                           int substeps, uint32_t flags, int layout, float* x_next);
+int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, int64_t B, int H,
+                      int substeps, uint32_t flags, int layout, float* X, float* x_final,
+                      float* cost, const AircCostParams* cost_params);
+int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
+                        int substeps, uint32_t flags, int layout, float* x_next, float* A,
+                        float* Bm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AIRCRAFT_B200_H */

@@ -1,0 +1,98 @@
+// host_emul.cpp -- TEST INFRASTRUCTURE ONLY (lives under oracle/, never linked into the product).
+//
+// Compiles the product's FP32 device formulas (aircraft_b200/csrc/airc_*.cuh, all AIRC_HD)
+// with g++ so that the `-m "not gpu"` tests can check the kernel arithmetic -- the folded
+// network, the rotation-matrix form, the forward-mode tangents -- against the float64 oracle
+// on a machine without a GPU.  MUFU approximations are replaced by libm here, so this checks
+// the algebra, not the last ulp; the GPU parity tests check the real thing.
+#include <stdint.h>
+
+#include "../aircraft_b200/csrc/airc_fuse.hpp"
+#include "../aircraft_b200/csrc/airc_step.cuh"
+
+using namespace airc;
+
+static void load(const float* x, const float* u, State& s, Ctl& c) {
+  for (int i = 0; i < 3; ++i) { s.p[i] = x[i]; s.v[i] = x[3 + i]; s.w[i] = x[10 + i]; }
+  for (int i = 0; i < 4; ++i) s.q[i] = x[6 + i];
+  c.da = u[0]; c.de = u[1]; c.dr = u[2]; c.df = u[6];
+}
+static void store(const State& s, float* x) {
+  for (int i = 0; i < 3; ++i) { x[i] = s.p[i]; x[3 + i] = s.v[i]; x[10 + i] = s.w[i]; }
+  for (int i = 0; i < 4; ++i) x[6 + i] = s.q[i];
+}
+
+extern "C" {
+
+void emul_fused_net(const AircNNBlob* nn, float* out /* sizeof(FusedNet)/4 floats */) {
+  FusedNet f;
+  fuse_network(*nn, f);
+  memcpy(out, &f, sizeof(f));
+}
+
+void emul_surrogate(const AircNNBlob* nn, const float* in5, int64_t n, float* out6) {
+  FusedNet f;
+  fuse_network(*nn, f);
+  for (int64_t i = 0; i < n; ++i) {
+    Ctl c{in5[5 * i + 3], in5[5 * i + 4], 0.f, 0.f};
+    float J[6][5];
+    surrogate<false>(f, in5[5 * i], in5[5 * i + 1], in5[5 * i + 2], c, out6 + 6 * i, J);
+  }
+}
+
+void emul_state_derivative(const AircParams* p, const AircNNBlob* nn, const float* x,
+                           const float* u, int64_t n, float* xdot) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c; Stage st; float J[6][5];
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* o = xdot + 13 * i;
+    f_eval<false>(P, s.v, s.q, s.w, c, o + 3, o + 6, o + 10, st, J);
+    for (int k = 0; k < 3; ++k) o[k] = s.v[k];
+  }
+}
+
+void emul_state_update(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                       float dt, int64_t n, int substeps, uint32_t flags, float* xn) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    state_update<0>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, nullptr);
+    store(s, xn + 13 * i);
+  }
+}
+
+// A[n][13][13], B[n][13][7]
+void emul_linearize(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                    float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                    float* Bm) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  for (int64_t i = 0; i < n; ++i) {
+    for (int col = 0; col < 20; ++col) {
+      State s; Ctl c;
+      load(x + 13 * i, u + 7 * i, s, c);
+      Tangent T;
+      memset(&T, 0, sizeof(T));
+      float* tp = &T.p[0];  // p,v,q,w are contiguous: 13 floats
+      if (col < 13) tp[col] = 1.0f;
+      else {
+        const int cu = col - 13;
+        if (cu == 0) T.dc.da = 1.0f;
+        if (cu == 1) T.dc.de = 1.0f;
+        if (cu == 2) T.dc.dr = 1.0f;
+        if (cu == 6) T.dc.df = 1.0f;
+      }
+      state_update<1>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, &T);
+      if (col == 0) store(s, xn + 13 * i);
+      for (int r = 0; r < 13; ++r) {
+        if (col < 13) A[(i * 13 + r) * 13 + col] = tp[r];
+        else Bm[(i * 13 + r) * 7 + (col - 13)] = tp[r];
+      }
+    }
+  }
+}
+}
