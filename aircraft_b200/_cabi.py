@@ -65,10 +65,12 @@ PROTOTYPES = {
     "airc_linearize": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                  _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
-    "airc_state_update_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _u32, _i32, _vp]),
+    "airc_state_derivative_host": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
+    "airc_state_update_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp]),
     "airc_rollout_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _i32, _vp, _vp,
                                     _vp, _CP]),
-    "airc_linearize_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _u32, _i32, _vp, _vp, _vp]),
+    "airc_linearize_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp,
+                                      _vp]),
 }
 
 _lib = None

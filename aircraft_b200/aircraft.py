@@ -1,0 +1,464 @@
+"""Host-side mirror of the reference's dynamics interface for the NN-surrogate hot path.
+
+Mirrors (names, argument meaning, orderings, error behaviour -- not code):
+  Aircraft(opts=AircraftOpts(...))        /root/reference/src/aircraft/dynamics/aircraft.py:105-121
+  .state_update(x, u, dt) -> x_next       /root/reference/src/aircraft/dynamics/base.py:450-480
+  .state_derivative(x, u) -> x_dot        /root/reference/src/aircraft/dynamics/base.py:385-406
+  .num_states / .num_controls             base.py:101 ; aircraft.py:162
+  .com / .normalise attributes set by the scripts after construction
+                                          main/control/control.py:168-172 ; control/base.py:182-185
+  COEFF_MODEL_REGISTRY / NeuralModel      /root/reference/src/aircraft/dynamics/coefficient_models.py:20-37,91-104
+
+Like a CasADi Function, state_update / state_derivative accept one column ([13], [7]) or a
+column-batched matrix ([13,N], [7,N]; CasADi maps the Function over columns) and return the
+same layout.  [13,N] row-major IS the kernels' native SoA layout, so no transpose happens.
+
+Everything numeric runs in the CUDA library through the C ABI (include/aircraft_b200.h).  There
+is no CPU fallback: without libaircraft_b200.so or without an sm_100 device this module raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from pathlib import Path
+from typing import Any, Callable, Dict, Optional, Sequence
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import (FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX)
+from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
+                     DEFAULT_PROBLEM_PATH)
+from .params import load_nn_blob, make_cost_params, make_params
+
+try:  # torch is plumbing (device memory, streams); the numpy/host path does not need it
+    import torch
+except Exception:  # pragma: no cover
+    torch = None
+
+
+class CoefficientModel:
+    """Plugin base, as coefficient_models.py:20-22."""
+
+    def __call__(self, inputs):
+        raise NotImplementedError
+
+
+class NeuralModel(CoefficientModel):
+    """The 'nn' registry entry (coefficient_models.py:91-104).  Holds the verbatim checkpoint;
+    the network itself is evaluated inside the fused kernels, so calling the model on its own
+    evaluates C = coefficients([qbar, alpha, beta, aileron, elevator]) through the library's
+    coefficient kernel."""
+
+    def __init__(self, path: Path | str, aircraft: "Aircraft", realtime: bool = False):
+        self.path = Path(path) if path else DEFAULT_MODEL_PATH
+        self.blob = load_nn_blob(self.path)
+        self.aircraft = aircraft
+
+
+def _unsupported(kind: str) -> Callable:
+    def factory(path, aircraft, **kw):
+        raise NotImplementedError(
+            f"coeff_model_type='{kind}' is outside the B200 hot path (SURVEY.md section 8a: only "
+            "the 'nn' surrogate is served); use the reference for this model")
+    return factory
+
+
+# same keys as the reference's registry; unknown keys fall back to 'default' there
+# (aircraft.py:37), which this build refuses loudly instead of silently changing the model.
+COEFF_MODEL_REGISTRY: Dict[str, Callable] = {
+    "nn": lambda path, aircraft, **kw: NeuralModel(path, aircraft, realtime=kw.get("realtime", False)),
+    "linear": _unsupported("linear"),
+    "poly": _unsupported("poly"),
+    "default": _unsupported("default"),
+}
+
+
+@dataclass
+class RolloutResult:
+    final: Any = None          # [B,13] (aos) or [13,B] (soa)
+    trajectory: Any = None     # [B,H+1,13] (aos) or [H+1,13,B] (soa)
+    cost: Any = None           # [B]
+
+
+def _check(rc: int, lib, what: str):
+    if rc != 0:
+        msg = lib.airc_last_error(None)
+        raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+def _is_torch(t) -> bool:
+    return torch is not None and isinstance(t, torch.Tensor)
+
+
+class Aircraft:
+    """B200 drop-in for the reference's ``Aircraft`` on the NN-surrogate path.
+
+    Differences a caller can see, all forced by the hardware path:
+      * arithmetic is FP32 on the GPU (results match the float64 reference to ~1e-6 per step);
+      * ``state_update`` / ``state_derivative`` are plain callables (no CasADi graph), so they
+        cannot be embedded symbolically into ``ca.Opti``; the Jacobians IPOPT would derive are
+        served by :meth:`linearize` instead;
+      * ``com`` and ``normalise`` may be assigned after construction exactly as the reference's
+        scripts do; the constant block is rebuilt on the next call.
+    """
+
+    num_states = NX
+    num_controls = NU
+
+    def __init__(self, opts: Optional[AircraftOpts] = None, *, com: Optional[Sequence[float]] = None,
+                 device: int | str | None = None, normalise: bool = False):
+        self.opts = opts if opts is not None else AircraftOpts(coeff_model_type="nn")
+        if self.opts.coeff_model_type not in COEFF_MODEL_REGISTRY:
+            raise NotImplementedError(f"unknown coeff_model_type {self.opts.coeff_model_type!r}")
+        cfg = self.opts.aircraft_config
+        self.S, self.b, self.c = cfg.reference_area, cfg.span, cfg.chord
+        self.mass = cfg.mass
+        self.grav = tuple(self.opts.gravity)
+        self.epsilon = self.opts.epsilon
+        self.physical_integration_substeps = int(self.opts.physical_integration_substeps)
+        self._com = tuple(float(c) for c in (cfg.aero_centre_offset if com is None else com))
+        self._stall_scaling = bool(self.opts.stall_scaling)
+        self.normalise = bool(normalise)
+        self.coefficient_model = COEFF_MODEL_REGISTRY[self.opts.coeff_model_type](
+            self.opts.coeff_model_path, self, realtime=self.opts.realtime)
+        self._device = self._parse_device(device)
+        self._lib = _cabi.load_library()      # raises ImportError when the .so is missing
+        self._handle = None
+
+    @classmethod
+    def from_problem(cls, path: Path | str = DEFAULT_PROBLEM_PATH, *, com=None, device=None,
+                     normalise: bool = False, coeff_model_path: Path | str = "", **opts_kw):
+        """Aircraft from the ``"aircraft"`` block of problem_definition.json with the 'nn' model,
+        as the reference's scripts build it (main/control/control.py:159-167)."""
+        opts = AircraftOpts(coeff_model_type="nn", coeff_model_path=coeff_model_path,
+                            aircraft_config=AircraftConfiguration.from_json(path), **opts_kw)
+        return cls(opts, com=com, device=device, normalise=normalise)
+
+    # ---- attributes the reference's scripts assign after construction
+    @property
+    def com(self):
+        return self._com
+
+    @com.setter
+    def com(self, value):
+        self._com = tuple(float(c) for c in np.asarray(value, np.float64).reshape(-1))
+        self._drop_handle()
+
+    @property
+    def stall_scaling(self):
+        return self._stall_scaling
+
+    @stall_scaling.setter
+    def stall_scaling(self, value):
+        self._stall_scaling = bool(value)
+        self._drop_handle()
+
+    @property
+    def device(self) -> int:
+        return self._device
+
+    @staticmethod
+    def _parse_device(device) -> int:
+        if device is None:
+            if torch is not None and torch.cuda.is_available():
+                return torch.cuda.current_device()
+            return 0
+        if isinstance(device, int):
+            return device
+        s = str(device)
+        if s == "cuda":
+            return 0
+        if s.startswith("cuda:"):
+            return int(s.split(":")[1])
+        raise ValueError(f"aircraft_b200 runs on CUDA devices only, got {device!r}")
+
+    # ---- handle management
+    def _drop_handle(self):
+        if getattr(self, "_handle", None):
+            self._lib.airc_destroy(self._handle)
+        self._handle = None
+
+    def __del__(self):
+        try:
+            self._drop_handle()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        if self._handle is None:
+            params = make_params(self.opts.aircraft_config, com=self._com, gravity=self.grav,
+                                 epsilon=self.epsilon, stall_scaling=self._stall_scaling)
+            params.mass = float(self.mass)
+            h = C.c_void_p()
+            rc = self._lib.airc_create(C.byref(params), C.byref(self.coefficient_model.blob),
+                                       self._device, C.byref(h))
+            _check(rc, self._lib, "airc_create")
+            self._handle = h
+        return self._handle
+
+    def _flags(self, normalise: Optional[bool]) -> int:
+        n = self.normalise if normalise is None else normalise
+        return FLAG_NORMALISE if n else 0
+
+    def _substeps(self, substeps: Optional[int]) -> int:
+        n = self.physical_integration_substeps if substeps is None else int(substeps)
+        if n < 1:
+            raise RuntimeError("physical_integration_substeps must be >= 1")
+        return n
+
+    # ---- tensor plumbing
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self._device).cuda_stream
+
+    def _dev32(self, t, name: str):
+        """float32 contiguous CUDA tensor on this aircraft's device (no copy when already so)."""
+        if t.device.type != "cuda" or t.device.index != self._device:
+            raise RuntimeError(f"{name} is on {t.device}, expected cuda:{self._device}")
+        return t.to(torch.float32).contiguous()
+
+    @staticmethod
+    def _host32(a, name: str) -> np.ndarray:
+        if _is_torch(a):
+            a = a.detach().cpu().numpy()
+        return np.ascontiguousarray(np.asarray(a), dtype=np.float32)
+
+    @staticmethod
+    def _ptr(a) -> int:
+        if a is None:
+            return None
+        return a.data_ptr() if _is_torch(a) else a.ctypes.data
+
+    def _on_device(self, *arrs) -> bool:
+        return any(_is_torch(a) and a.device.type == "cuda" for a in arrs)
+
+    # ------------------------------------------------------------------ CasADi-style callables
+    def _columns(self, x, u):
+        """Validate CasADi-style column arguments; returns (x2[13,N], u2[7,N], N, squeeze)."""
+        if _is_torch(x) or _is_torch(u):
+            as2 = lambda a, rows: (a if _is_torch(a) else torch.as_tensor(np.asarray(a)))
+            x2, u2 = as2(x, NX), as2(u, NU)
+            if x2.device != u2.device:
+                dev = x2.device if x2.device.type == "cuda" else u2.device
+                x2, u2 = x2.to(dev), u2.to(dev)
+        else:
+            x2, u2 = np.asarray(x), np.asarray(u)
+        squeeze = x2.ndim == 1 and u2.ndim == 1
+        if x2.ndim == 1:
+            x2 = x2.reshape(NX, 1) if x2.shape[0] == NX else x2
+        if u2.ndim == 1:
+            u2 = u2.reshape(NU, 1) if u2.shape[0] == NU else u2
+        if x2.ndim != 2 or x2.shape[0] != NX:
+            raise RuntimeError(f"state must have shape [13] or [13,N], got {tuple(x2.shape)}")
+        if u2.ndim != 2 or u2.shape[0] != NU:
+            raise RuntimeError(f"control must have shape [7] or [7,N], got {tuple(u2.shape)}")
+        n = max(x2.shape[1], u2.shape[1])
+        for name, a in (("state", x2), ("control", u2)):
+            if a.shape[1] not in (1, n):
+                raise RuntimeError(f"{name} has {a.shape[1]} columns, expected 1 or {n}")
+        if x2.shape[1] != n:   # CasADi's map repeats single-column arguments
+            x2 = x2.expand(NX, n) if _is_torch(x2) else np.broadcast_to(x2, (NX, n))
+        if u2.shape[1] != n:
+            u2 = u2.expand(NU, n) if _is_torch(u2) else np.broadcast_to(u2, (NU, n))
+        return x2, u2, n, squeeze
+
+    def _dt_args(self, dt, n: int, on_device: bool):
+        """(scalar dt, per-node array or None)."""
+        if _is_torch(dt):
+            if dt.numel() == 1:
+                return float(dt.item()), None
+            d = dt.reshape(-1)
+        else:
+            d = np.asarray(dt, np.float64).reshape(-1)
+            if d.size == 1:
+                return float(d[0]), None
+        if d.shape[0] != n:
+            raise RuntimeError(f"dt has {d.shape[0]} entries, expected 1 or {n}")
+        if on_device:
+            d = d if _is_torch(d) else torch.as_tensor(d)
+            return 0.0, d.to(device=f"cuda:{self._device}", dtype=torch.float32).contiguous()
+        return 0.0, self._host32(d, "dt")
+
+    def state_derivative(self, x, u):
+        """f(x,u): the reference's ca.Function 'dynamics' (base.py:402-406)."""
+        x2, u2, n, squeeze = self._columns(x, u)
+        lib, h = self._lib, self.handle
+        if self._on_device(x2, u2):
+            xd, ud = self._dev32(x2, "x"), self._dev32(u2, "u")
+            out = torch.empty((NX, n), dtype=torch.float32, device=xd.device)
+            _check(lib.airc_state_derivative(h, xd.data_ptr(), ud.data_ptr(), n, LAYOUT_SOA,
+                                             out.data_ptr(), self._stream()), lib, "airc_state_derivative")
+        else:
+            xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
+            out = np.empty((NX, n), np.float32)
+            _check(lib.airc_state_derivative_host(h, xh.ctypes.data, uh.ctypes.data, n, LAYOUT_SOA,
+                                                  out.ctypes.data), lib, "airc_state_derivative_host")
+            out = self._like(out, x)
+        return out[:, 0] if squeeze else out
+
+    def state_update(self, x, u, dt, *, substeps: Optional[int] = None,
+                     normalise: Optional[bool] = None):
+        """Phi(x,u,dt): the reference's ca.Function 'state_update' (base.py:476-480).
+        n = physical_integration_substeps RK4 steps of dt/n; quaternion normalised once at the end
+        when ``normalise`` (base.py:466-474)."""
+        x2, u2, n, squeeze = self._columns(x, u)
+        lib, h = self._lib, self.handle
+        on_dev = self._on_device(x2, u2)
+        dts, dtn = self._dt_args(dt, n, on_dev)
+        ns, fl = self._substeps(substeps), self._flags(normalise)
+        if on_dev:
+            xd, ud = self._dev32(x2, "x"), self._dev32(u2, "u")
+            out = torch.empty((NX, n), dtype=torch.float32, device=xd.device)
+            _check(lib.airc_state_update(h, xd.data_ptr(), ud.data_ptr(), dts, self._ptr(dtn), n, ns,
+                                         fl, LAYOUT_SOA, out.data_ptr(), self._stream()),
+                   lib, "airc_state_update")
+        else:
+            xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
+            out = np.empty((NX, n), np.float32)
+            _check(lib.airc_state_update_host(h, xh.ctypes.data, uh.ctypes.data, dts, self._ptr(dtn),
+                                              n, ns, fl, LAYOUT_SOA, out.ctypes.data),
+                   lib, "airc_state_update_host")
+            out = self._like(out, x)
+        return out[:, 0] if squeeze else out
+
+    @staticmethod
+    def _like(out: np.ndarray, ref):
+        """Host results come back in the caller's container and float dtype (the reference hands
+        back float64 DM values; FP32 results are widened, not recomputed)."""
+        if _is_torch(ref):
+            t = torch.from_numpy(out)
+            return t.to(ref.dtype) if ref.dtype.is_floating_point else t
+        dt = getattr(ref, "dtype", None)
+        if dt is not None and np.issubdtype(dt, np.floating):
+            return out.astype(dt, copy=False)
+        return out.astype(np.float64)
+
+    # ------------------------------------------------------------------ batched-native entry points
+    def rollout(self, x0, U, dt: float, *, substeps: Optional[int] = None,
+                normalise: Optional[bool] = None, layout: str = "aos",
+                return_trajectory: bool = False, return_final: bool = True,
+                cost=None) -> RolloutResult:
+        """x[k+1] = Phi(x[k], u[k], dt) for k < H over B independent trajectories in ONE kernel:
+        the reference's Python loops (main/control/control.py:84-90,
+        control/moving_horizon.py:208-213, main/dynamics/dynamics.py:105-121).
+
+        layout 'aos': x0[B,13], U[B,H,7] (or one shared sequence U[H,7]);
+                      trajectory [B,H+1,13], final [B,13]
+        layout 'soa': x0[13,B], U[H,7,B] (or U[H,7]); trajectory [H+1,13,B], final [13,B]
+                      (batch index fastest: the kernels' native, fully coalesced layout)
+        cost: None, True (default weights), a dict of make_cost_params kwargs or an
+              AircCostParams -> per-trajectory primary MPC loss (main/control/control.py:35-70).
+        """
+        if layout not in ("aos", "soa"):
+            raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
+        soa = layout == "soa"
+        on_dev = self._on_device(x0, U)
+        if on_dev:
+            x0d = self._dev32(x0 if _is_torch(x0) else torch.as_tensor(x0).cuda(self._device), "x0")
+            Ud = self._dev32(U if _is_torch(U) else torch.as_tensor(U).cuda(self._device), "U")
+        else:
+            x0d, Ud = self._host32(x0, "x0"), self._host32(U, "U")
+        if x0d.ndim != 2 or x0d.shape[0 if soa else 1] != NX:
+            raise RuntimeError(f"x0 must be {'[13,B]' if soa else '[B,13]'}, got {tuple(x0d.shape)}")
+        B = x0d.shape[1 if soa else 0]
+        flags = self._flags(normalise)
+        if Ud.ndim == 2:
+            if Ud.shape[1] != NU:
+                raise RuntimeError(f"shared control sequence must be [H,7], got {tuple(Ud.shape)}")
+            H = Ud.shape[0]
+            flags |= FLAG_SHARED_U
+        elif Ud.ndim == 3:
+            ok = (Ud.shape[1] == NU and Ud.shape[2] == B) if soa else (Ud.shape[0] == B and Ud.shape[2] == NU)
+            if not ok:
+                raise RuntimeError(f"U must be {'[H,7,B]' if soa else '[B,H,7]'}, got {tuple(Ud.shape)}")
+            H = Ud.shape[0] if soa else Ud.shape[1]
+        else:
+            raise RuntimeError(f"U must have 2 or 3 dimensions, got {tuple(Ud.shape)}")
+        cp = None
+        if cost is not None and cost is not False:
+            cp = cost if isinstance(cost, _cabi.AircCostParams) else \
+                make_cost_params(**(cost if isinstance(cost, dict) else {}))
+        shp_X = (H + 1, NX, B) if soa else (B, H + 1, NX)
+        shp_f = (NX, B) if soa else (B, NX)
+        if on_dev:
+            mk = lambda s: torch.empty(s, dtype=torch.float32, device=x0d.device)
+        else:
+            mk = lambda s: np.empty(s, np.float32)
+        X = mk(shp_X) if return_trajectory else None
+        xf = mk(shp_f) if return_final else None
+        cst = mk((B,)) if cp is not None else None
+        lib, h = self._lib, self.handle
+        cpp = C.byref(cp) if cp is not None else None
+        lay = LAYOUT_SOA if soa else LAYOUT_AOS
+        ns = self._substeps(substeps)
+        if on_dev:
+            _check(lib.airc_rollout(h, x0d.data_ptr(), Ud.data_ptr(), float(dt), B, H, ns, flags, lay,
+                                    self._ptr(X), self._ptr(xf), self._ptr(cst), cpp, self._stream()),
+                   lib, "airc_rollout")
+        else:
+            _check(lib.airc_rollout_host(h, x0d.ctypes.data, Ud.ctypes.data, float(dt), B, H, ns, flags,
+                                         lay, self._ptr(X), self._ptr(xf), self._ptr(cst), cpp),
+                   lib, "airc_rollout_host")
+            X, xf, cst = (None if a is None else self._like(a, x0) for a in (X, xf, cst))
+        return RolloutResult(final=xf, trajectory=X, cost=cst)
+
+    def linearize(self, x, u, dt, *, substeps: Optional[int] = None,
+                  normalise: Optional[bool] = None, layout: str = "aos",
+                  want_next: bool = True):
+        """(x_next, A = dPhi/dx, B = dPhi/du) at every node by forward-mode tangents: what the
+        reference obtains from ca.jacobian(state_update, x|u) (control/aircraft.py:85-95,
+        base.py:51-52, main/stability/stability.py:48-54) and IPOPT from the defect constraints
+        (control/base.py:275-286).
+
+        layout 'aos': x[...,13], u[...,7] -> x_next[...,13], A[...,13,13], B[...,13,7]
+        layout 'soa': x[13,N],  u[7,N]   -> x_next[13,N],  A[13,13,N],  B[13,7,N]
+        """
+        if layout not in ("aos", "soa"):
+            raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
+        soa = layout == "soa"
+        on_dev = self._on_device(x, u)
+        if on_dev:
+            xd = self._dev32(x if _is_torch(x) else torch.as_tensor(x).cuda(self._device), "x")
+            ud = self._dev32(u if _is_torch(u) else torch.as_tensor(u).cuda(self._device), "u")
+        else:
+            xd, ud = self._host32(x, "x"), self._host32(u, "u")
+        if soa:
+            if xd.ndim != 2 or xd.shape[0] != NX or ud.ndim != 2 or ud.shape[0] != NU or \
+                    xd.shape[1] != ud.shape[1]:
+                raise RuntimeError(f"soa linearize wants x[13,N], u[7,N]; got {tuple(xd.shape)}, {tuple(ud.shape)}")
+            lead, n = (xd.shape[1],), xd.shape[1]
+            shp_x, shp_A, shp_B = (NX, n), (NX, NX, n), (NX, NU, n)
+        else:
+            if xd.shape[-1] != NX or ud.shape[-1] != NU or xd.shape[:-1] != ud.shape[:-1]:
+                raise RuntimeError(f"aos linearize wants x[...,13], u[...,7]; got {tuple(xd.shape)}, {tuple(ud.shape)}")
+            lead = tuple(xd.shape[:-1])
+            n = int(np.prod(lead)) if lead else 1
+            shp_x, shp_A, shp_B = lead + (NX,), lead + (NX, NX), lead + (NX, NU)
+        dts, dtn = self._dt_args(dt, n, on_dev)
+        mk = (lambda s: torch.empty(s, dtype=torch.float32, device=xd.device)) if on_dev else \
+            (lambda s: np.empty(s, np.float32))
+        xn = mk(shp_x) if want_next else None
+        A, Bm = mk(shp_A), mk(shp_B)
+        lib, h = self._lib, self.handle
+        lay = LAYOUT_SOA if soa else LAYOUT_AOS
+        ns, fl = self._substeps(substeps), self._flags(normalise)
+        if on_dev:
+            _check(lib.airc_linearize(h, xd.data_ptr(), ud.data_ptr(), dts, self._ptr(dtn), n, ns, fl,
+                                      lay, self._ptr(xn), A.data_ptr(), Bm.data_ptr(), self._stream()),
+                   lib, "airc_linearize")
+        else:
+            _check(lib.airc_linearize_host(h, xd.ctypes.data, ud.ctypes.data, dts, self._ptr(dtn), n,
+                                           ns, fl, lay, self._ptr(xn), A.ctypes.data, Bm.ctypes.data),
+                   lib, "airc_linearize_host")
+            xn, A, Bm = (None if a is None else self._like(a, x) for a in (xn, A, Bm))
+        return xn, A, Bm
+
+    def argmin(self, cost):
+        """(min, argmin) of a device cost vector; ties resolve to the lower index, NaNs sort last."""
+        c = self._dev32(cost, "cost").reshape(-1)
+        out_min = torch.empty(1, dtype=torch.float32, device=c.device)
+        out_idx = torch.empty(1, dtype=torch.int64, device=c.device)
+        _check(self._lib.airc_argmin(self.handle, c.data_ptr(), c.numel(), out_min.data_ptr(),
+                                     out_idx.data_ptr(), self._stream()), self._lib, "airc_argmin")
+        return out_min, out_idx

@@ -231,9 +231,9 @@ static int ensure_scratch(AircHandle* h, size_t bytes) {
 
 static size_t al(size_t n_floats) { return ((n_floats * sizeof(float) + 255) / 256) * 256; }
 
-int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
-                           int substeps, uint32_t flags, int layout, float* x_next) {
-  if (!h || !x || !u || !x_next || n < 0) return fail(AIRC_EINVAL, "airc_state_update_host: bad argument%s", "");
+int airc_state_derivative_host(AircHandle* h, const float* x, const float* u, int64_t n, int layout,
+                               float* xdot) {
+  if (!h || !x || !u || !xdot || n < 0) return fail(AIRC_EINVAL, "airc_state_derivative_host: bad argument%s", "");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
@@ -244,7 +244,30 @@ int airc_state_update_host(AircHandle* h, const float* x, const float* u, float 
   float *dx = (float*)base, *du = (float*)(base + bx), *dn = (float*)(base + bx + bu);
   CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
   CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
-  rc = airc_state_update(h, dx, du, dt, nullptr, n, substeps, flags, layout, dn, h->hstream);
+  rc = airc_state_derivative(h, dx, du, n, layout, dn, h->hstream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(xdot, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
+int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt,
+                           const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                           int layout, float* x_next) {
+  if (!h || !x || !u || !x_next || n < 0) return fail(AIRC_EINVAL, "airc_state_update_host: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t bx = al(13 * n), bu = al(7 * n), bd = dt_per_node ? al(n) : 0;
+  int rc = ensure_scratch(h, 2 * bx + bu + bd);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float *dx = (float*)base, *du = (float*)(base + bx), *dn = (float*)(base + bx + bu);
+  float* ddt = dt_per_node ? (float*)(base + 2 * bx + bu) : nullptr;
+  CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  if (ddt) CUDA_TRY(cudaMemcpyAsync(ddt, dt_per_node, n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_state_update(h, dx, du, dt, ddt, n, substeps, flags, layout, dn, h->hstream);
   if (rc) return rc;
   CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   CUDA_TRY(cudaStreamSynchronize(h->hstream));
@@ -280,15 +303,16 @@ int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, 
   return AIRC_OK;
 }
 
-int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
-                        int substeps, uint32_t flags, int layout, float* x_next, float* A,
-                        float* Bm) {
+int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
+                        const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                        int layout, float* x_next, float* A, float* Bm) {
   if (!h || !x || !u || n < 0) return fail(AIRC_EINVAL, "airc_linearize_host: bad argument%s", "");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   const size_t bx = al(13 * n), bu = al(7 * n), bA = A ? al(169 * n) : 0, bB = Bm ? al(91 * n) : 0;
-  int rc = ensure_scratch(h, 2 * bx + bu + bA + bB);
+  const size_t bd = dt_per_node ? al(n) : 0;
+  int rc = ensure_scratch(h, 2 * bx + bu + bA + bB + bd);
   if (rc) return rc;
   char* base = (char*)h->scratch;
   float* dx = (float*)base;
@@ -296,9 +320,11 @@ int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
   float* dn = x_next ? (float*)(base + bx + bu) : nullptr;
   float* dA = A ? (float*)(base + 2 * bx + bu) : nullptr;
   float* dB = Bm ? (float*)(base + 2 * bx + bu + bA) : nullptr;
+  float* ddt = dt_per_node ? (float*)(base + 2 * bx + bu + bA + bB) : nullptr;
+  if (ddt) CUDA_TRY(cudaMemcpyAsync(ddt, dt_per_node, n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
   CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
   CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
-  rc = airc_linearize(h, dx, du, dt, nullptr, n, substeps, flags, layout, dn, dA, dB, h->hstream);
+  rc = airc_linearize(h, dx, du, dt, ddt, n, substeps, flags, layout, dn, dA, dB, h->hstream);
   if (rc) return rc;
   if (x_next) CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   if (A) CUDA_TRY(cudaMemcpyAsync(A, dA, 169 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));

@@ -153,14 +153,17 @@ int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_mi
 /* Convenience for FFI callers that hold HOST buffers (the cgo/ctypes style binding a maintainer
  * of the reference would use from numpy): allocates device scratch, copies in, runs, copies out,
  * synchronises.  Same semantics as the device-pointer versions. */
-int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
-                           int substeps, uint32_t flags, int layout, float* x_next);
+int airc_state_derivative_host(AircHandle* h, const float* x, const float* u, int64_t n, int layout,
+                               float* xdot);
+int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt,
+                           const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                           int layout, float* x_next);
 int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, int64_t B, int H,
                       int substeps, uint32_t flags, int layout, float* X, float* x_final,
                       float* cost, const AircCostParams* cost_params);
-int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt, int64_t n,
-                        int substeps, uint32_t flags, int layout, float* x_next, float* A,
-                        float* Bm);
+int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
+                        const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                        int layout, float* x_next, float* A, float* Bm);
 
 #ifdef __cplusplus
 }

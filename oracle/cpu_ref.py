@@ -1,0 +1,127 @@
+"""ctypes loaders for the two C++ checkers built by oracle/Makefile -- TEST INFRASTRUCTURE.
+
+  libairc_cpu_ref.so    float64 as-written restatement of the reference path, OpenMP
+                        (oracle/cpu_ref.cpp): the timed CPU baseline, validated against
+                        oracle/aircraft_oracle.py
+  libairc_host_emul.so  the product's own FP32 device formulas compiled with g++
+                        (oracle/host_emul.cpp): lets the CPU-only tests check the kernel algebra
+"""
+from __future__ import annotations
+
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+from aircraft_b200._cabi import AircNNBlob, AircParams
+
+HERE = Path(__file__).resolve().parent
+_f64 = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+_f32 = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+_PP, _NP = C.POINTER(AircParams), C.POINTER(AircNNBlob)
+
+
+def _load(name: str) -> C.CDLL:
+    p = HERE / name
+    if not p.exists():
+        r = subprocess.run(["make", "-C", str(HERE)], capture_output=True, text=True)
+        if r.returncode != 0 or not p.exists():
+            raise RuntimeError(f"cannot build {name}:\n{r.stdout}{r.stderr}")
+    return C.CDLL(str(p))
+
+
+class CpuRef:
+    """float64 OpenMP restatement (cpu_ref.cpp).  Arrays are AoS: x[n,13], u[n,7]."""
+
+    def __init__(self, params: AircParams, blob: AircNNBlob, threads: int = 0):
+        self.lib = _load("libairc_cpu_ref.so")
+        self.params, self.blob = params, blob
+        self.lib.cpuref_max_threads.restype = C.c_int
+        self.max_threads = int(self.lib.cpuref_max_threads())
+        self.threads = threads if threads > 0 else self.max_threads
+        vp = C.c_void_p
+        self.lib.cpuref_state_derivative.argtypes = [_PP, _NP, _f64, _f64, C.c_int64, _f64, C.c_int]
+        self.lib.cpuref_state_update.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
+                                                 C.c_uint32, _f64, C.c_int]
+        self.lib.cpuref_rollout.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
+                                            C.c_int, C.c_uint32, vp, vp, C.c_int]
+        self.lib.cpuref_linearize.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
+                                              C.c_uint32, _f64, _f64, _f64, C.c_int]
+
+    def _pb(self):
+        return C.byref(self.params), C.byref(self.blob)
+
+    def state_derivative(self, x, u):
+        x, u = np.ascontiguousarray(x, np.float64), np.ascontiguousarray(u, np.float64)
+        out = np.empty_like(x)
+        self.lib.cpuref_state_derivative(*self._pb(), x, u, x.shape[0], out, self.threads)
+        return out
+
+    def state_update(self, x, u, dt, substeps=1, normalise=False):
+        x, u = np.ascontiguousarray(x, np.float64), np.ascontiguousarray(u, np.float64)
+        out = np.empty_like(x)
+        self.lib.cpuref_state_update(*self._pb(), x, u, float(dt), x.shape[0], substeps,
+                                     1 if normalise else 0, out, self.threads)
+        return out
+
+    def rollout(self, x0, U, dt, substeps=1, normalise=False, trajectory=True):
+        x0, U = np.ascontiguousarray(x0, np.float64), np.ascontiguousarray(U, np.float64)
+        B = x0.shape[0]
+        flags = (1 if normalise else 0) | (2 if U.ndim == 2 else 0)
+        H = U.shape[0] if U.ndim == 2 else U.shape[1]
+        X = np.empty((B, H + 1, 13)) if trajectory else None
+        xf = np.empty((B, 13))
+        self.lib.cpuref_rollout(*self._pb(), x0, U, float(dt), B, H, substeps, flags,
+                                X.ctypes.data if trajectory else None, xf.ctypes.data, self.threads)
+        return X if trajectory else xf
+
+    def linearize(self, x, u, dt, substeps=1, normalise=False):
+        x, u = np.ascontiguousarray(x, np.float64), np.ascontiguousarray(u, np.float64)
+        n = x.shape[0]
+        xn, A, Bm = np.empty((n, 13)), np.empty((n, 13, 13)), np.empty((n, 13, 7))
+        self.lib.cpuref_linearize(*self._pb(), x, u, float(dt), n, substeps, 1 if normalise else 0,
+                                  xn, A, Bm, self.threads)
+        return xn, A, Bm
+
+
+class HostEmul:
+    """The product's FP32 formulas on the CPU (host_emul.cpp).  AoS float32 arrays."""
+
+    def __init__(self, params: AircParams, blob: AircNNBlob):
+        self.lib = _load("libairc_host_emul.so")
+        self.params, self.blob = params, blob
+        self.lib.emul_surrogate.argtypes = [_NP, _f32, C.c_int64, _f32]
+        self.lib.emul_state_derivative.argtypes = [_PP, _NP, _f32, _f32, C.c_int64, _f32]
+        self.lib.emul_state_update.argtypes = [_PP, _NP, _f32, _f32, C.c_float, C.c_int64, C.c_int,
+                                               C.c_uint32, _f32]
+        self.lib.emul_linearize.argtypes = [_PP, _NP, _f32, _f32, C.c_float, C.c_int64, C.c_int,
+                                            C.c_uint32, _f32, _f32, _f32]
+
+    def surrogate(self, inp):
+        inp = np.ascontiguousarray(inp, np.float32)
+        out = np.empty((inp.shape[0], 6), np.float32)
+        self.lib.emul_surrogate(C.byref(self.blob), inp, inp.shape[0], out)
+        return out
+
+    def state_derivative(self, x, u):
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        out = np.empty_like(x)
+        self.lib.emul_state_derivative(C.byref(self.params), C.byref(self.blob), x, u, x.shape[0], out)
+        return out
+
+    def state_update(self, x, u, dt, substeps=1, normalise=False):
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        out = np.empty_like(x)
+        self.lib.emul_state_update(C.byref(self.params), C.byref(self.blob), x, u, float(dt),
+                                   x.shape[0], substeps, 1 if normalise else 0, out)
+        return out
+
+    def linearize(self, x, u, dt, substeps=1, normalise=False):
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        n = x.shape[0]
+        xn = np.empty((n, 13), np.float32)
+        A, Bm = np.zeros((n, 13, 13), np.float32), np.zeros((n, 13, 7), np.float32)
+        self.lib.emul_linearize(C.byref(self.params), C.byref(self.blob), x, u, float(dt), n, substeps,
+                                1 if normalise else 0, xn, A, Bm)
+        return xn, A, Bm

@@ -1,0 +1,52 @@
+"""CPU-side check of the PRODUCT's FP32 formulas (folded network, rotation-matrix form,
+forward-mode tangents, RK4 with tangents) compiled with g++ from the very headers the kernels
+use (oracle/host_emul.cpp), against the float64 oracle at the 1e-5 parity bar.  The MUFU
+approximations are libm here; the -m gpu tests check the real device arithmetic."""
+import numpy as np
+import pytest
+
+from _util import PARITY_TOL, col_err, oracle_for, params_for, t64
+from aircraft_b200.workloads import make_controls, make_states
+from oracle.cpu_ref import HostEmul
+
+
+@pytest.fixture(scope="module")
+def pair(built, com):
+    p, blob = params_for(com)
+    return HostEmul(p, blob), oracle_for(com)
+
+
+def test_folded_surrogate_vs_reference_module(built, golden_dir):
+    """W21 = W2.W1 with scalers folded in float64, logistic form of tanh: equal to the reference's
+    ScaledModel on the golden inputs."""
+    g = np.load(golden_dir / "nn_golden.npz")
+    p, blob = params_for()
+    got = HostEmul(p, blob).surrogate(g["inputs"])
+    assert col_err(got, g["out_f64"], atol=1e-4) < PARITY_TOL
+
+
+def test_state_derivative(pair):
+    emu, orc = pair
+    x, u = make_states(4096, seed=21, perturb_norm=1e-3), make_controls(4096, seed=21)
+    want = orc.state_derivative(t64(x), t64(u)).numpy()
+    assert col_err(emu.state_derivative(x, u), want) < PARITY_TOL
+
+
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (10, True)])
+def test_state_update(pair, substeps, normalise):
+    emu, orc = pair
+    x, u = make_states(2048, seed=22), make_controls(2048, seed=22)
+    want = orc.state_update(t64(x), t64(u), 0.01, substeps, normalise).numpy()
+    assert col_err(emu.state_update(x, u, 0.01, substeps, normalise), want) < PARITY_TOL
+
+
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (2, True)])
+def test_linearize(pair, substeps, normalise):
+    emu, orc = pair
+    x, u = make_states(512, seed=23, perturb_norm=1e-3), make_controls(512, seed=23)
+    xn, A, B = emu.linearize(x, u, 0.01, substeps, normalise)
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01, substeps, normalise)
+    assert col_err(xn, xo.numpy()) < PARITY_TOL
+    # Jacobian entries: per-entry scale over the batch, floor 1e-3 of the matrix scale
+    assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
