@@ -1,0 +1,134 @@
+"""Data-parallel sharding of independent rollouts / linearisation nodes over the GPUs of one box.
+
+The reference has no parallelism at all; every rollout and every (x,u)
+node is independent, so the batch is cut into contiguous slices, one per rank (one process per
+GPU), with no data-path traffic.  The only exchange is the final one north_star asks for:
+all ranks learn (min cost, global arg-min) and receive the winner's trajectory and control
+sequence -- one all_gather of 16 bytes per rank plus one broadcast of ~16 kB over NCCL/NVLink.
+All costs can optionally be gathered (4 B per trajectory).
+
+The collective helpers take CPU tensors under gloo as well, which is how the N>1 logic is tested
+without GPUs (tests/test_sharding.py).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous [start, stop) of `total` items for `rank`; the remainder goes to the lowest ranks."""
+    if world < 1 or not (0 <= rank < world) or total < 0:
+        raise ValueError(f"bad shard request total={total} rank={rank} world={world}")
+    base, rem = divmod(total, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+def _orderable(cost: torch.Tensor) -> torch.Tensor:
+    """float32 -> int64 key that sorts like the float (NaN last); same mapping as the argmin kernel."""
+    bits = cost.detach().to(torch.float32).contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    neg = (bits & 0x80000000) != 0
+    key = torch.where(neg, (~bits) & 0xFFFFFFFF, bits | 0x80000000)
+    return torch.where(torch.isnan(cost.to(torch.float32)), torch.full_like(key, 0xFFFFFFFF), key)
+
+
+def global_argmin(local_min: torch.Tensor, local_global_idx: torch.Tensor,
+                  group=None) -> Tuple[torch.Tensor, int, int]:
+    """(min cost, global index, owner-independent) over all ranks.  Ties resolve to the lower
+    global index, so the result does not depend on how the batch was sharded."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    pair = torch.stack([_orderable(local_min.reshape(1))[0], local_global_idx.reshape(1)[0].to(torch.int64)])
+    vals = torch.stack([local_min.reshape(1)[0].to(torch.float32)])
+    if world == 1:
+        return vals[0], int(pair[1].item()), 0
+    pairs = [torch.empty_like(pair) for _ in range(world)]
+    mins = [torch.empty_like(vals) for _ in range(world)]
+    dist.all_gather(pairs, pair, group=group)
+    dist.all_gather(mins, vals, group=group)
+    keys = torch.stack(pairs).cpu()
+    best = min(range(world), key=lambda r: (int(keys[r, 0]), int(keys[r, 1])))
+    return mins[best][0], int(keys[best, 1]), best
+
+
+@dataclass
+class SweepResult:
+    min_cost: float
+    argmin: int                      # global trajectory index
+    owner: int                       # rank that held it
+    best_trajectory: Any             # [H+1,13] on every rank
+    best_controls: Any               # [H,7] on every rank
+    local_cost: Any                  # this rank's costs [stop-start]
+    all_cost: Optional[Any] = None   # [B] on every rank when gather_costs
+
+
+class ShardedRollout:
+    """Sampling-MPC sweep (BASELINE config 4): B control sequences from one or many initial
+    states, sharded over the ranks of the default process group."""
+
+    def __init__(self, aircraft, group=None):
+        self.aircraft = aircraft
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+
+    def local_range(self, total: int) -> Tuple[int, int]:
+        return shard_range(total, self.rank, self.world)
+
+    def sweep(self, x0_local, U_local, dt: float, total: int, *, cost=True, layout: str = "soa",
+              substeps: Optional[int] = None, normalise: Optional[bool] = None,
+              gather_costs: bool = False) -> SweepResult:
+        """x0_local / U_local hold this rank's slice [start, stop) of the `total` rollouts in the
+        given layout.  Runs the fused rollout+cost kernel, reduces (min, arg-min) on the device,
+        exchanges it, and hands every rank the winner's trajectory (re-rolled by its owner: one
+        extra single-trajectory launch instead of storing B trajectories)."""
+        ac = self.aircraft
+        start, stop = self.local_range(total)
+        res = ac.rollout(x0_local, U_local, dt, substeps=substeps, normalise=normalise, layout=layout,
+                         return_final=False, cost=cost)
+        lmin, lidx = ac.argmin(res.cost)
+        gmin, gidx, owner = global_argmin(lmin, lidx + start, self.group)
+        soa = layout == "soa"
+        shared = U_local.ndim == 2
+        H = U_local.shape[0] if (soa or shared) else U_local.shape[1]
+        dev = res.cost.device
+        traj = torch.empty((H + 1, 13), dtype=torch.float32, device=dev)
+        ctrl = torch.empty((H, 7), dtype=torch.float32, device=dev)
+        if owner == self.rank:
+            j = gidx - start
+            xb = (x0_local[:, j] if soa else x0_local[j]).reshape(1, 13).contiguous()
+            ub = U_local if shared else (U_local[:, :, j] if soa else U_local[j])
+            ub = ub.reshape(H, 7).contiguous()
+            one = ac.rollout(xb, ub, dt, substeps=substeps, normalise=normalise, layout="aos",
+                             return_trajectory=True, return_final=False)
+            traj.copy_(one.trajectory[0])
+            ctrl.copy_(ub)
+        all_cost = None
+        if self.world > 1:
+            dist.broadcast(traj, src=dist.get_global_rank(self.group, owner) if self.group else owner,
+                           group=self.group)
+            dist.broadcast(ctrl, src=dist.get_global_rank(self.group, owner) if self.group else owner,
+                           group=self.group)
+        if gather_costs:
+            all_cost = gather_varlen(res.cost, total, self.rank, self.world, self.group)
+        return SweepResult(float(gmin), gidx, owner, traj, ctrl, res.cost, all_cost)
+
+
+def gather_varlen(local: torch.Tensor, total: int, rank: int, world: int, group=None) -> torch.Tensor:
+    """all_gather of contiguous shards whose lengths follow shard_range (differ by at most one)."""
+    if world == 1:
+        return local
+    longest = shard_range(total, 0, world)
+    pad = longest[1] - longest[0]
+    buf = torch.zeros(pad, dtype=local.dtype, device=local.device)
+    buf[: local.numel()] = local
+    out = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(out, buf, group=group)
+    parts = []
+    for r in range(world):
+        a, b = shard_range(total, r, world)
+        parts.append(out[r][: b - a])
+    return torch.cat(parts)

@@ -1,0 +1,124 @@
+"""Jacobian parity (K2) and full-size property tests on the GPU, through the C ABI."""
+import numpy as np
+import pytest
+import torch
+
+from _util import PARITY_TOL, col_err, oracle_for, t64
+from aircraft_b200.config import TRIM_COM
+from aircraft_b200.workloads import make_control_sequences, make_controls, make_states
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def f32(a):
+    return torch.tensor(np.asarray(a), dtype=torch.float32, device=DEV)
+
+
+@pytest.fixture(scope="module")
+def ac(built):
+    from aircraft_b200 import Aircraft
+    return Aircraft.from_problem(com=TRIM_COM, device=DEV, physical_integration_substeps=1)
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return oracle_for(TRIM_COM)
+
+
+@pytest.mark.parametrize("substeps,normalise,dt", [(1, False, 0.01), (1, True, 0.01), (3, True, 0.03)])
+def test_linearize_parity(ac, orc, substeps, normalise, dt):
+    n = 4096
+    x, u = make_states(n, seed=41, perturb_norm=1e-3), make_controls(n, seed=41)
+    xn, A, B = ac.linearize(f32(x), f32(u), dt, substeps=substeps, normalise=normalise)
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), dt, substeps, normalise)
+    assert col_err(xn.cpu(), xo.numpy()) < PARITY_TOL
+    assert col_err(A.cpu(), Ao.numpy()) < PARITY_TOL
+    assert col_err(B.cpu(), Bo.numpy()) < PARITY_TOL
+
+
+def test_linearize_structure_and_layouts(ac):
+    n = 1001
+    x, u = make_states(n, seed=42, perturb_norm=1e-3), make_controls(n, seed=42)
+    xn, A, B = ac.linearize(f32(x), f32(u), 0.01)
+    eye = torch.eye(13, device=DEV)[:, :3]
+    assert torch.equal(A[:, :, :3], eye.expand(n, 13, 3))      # dPhi/dp = [I;0] exactly
+    assert torch.count_nonzero(B[:, :, 3:6]) == 0              # thrust is inert (aircraft.py:320)
+    assert torch.equal(xn, ac.state_update(f32(x.T), f32(u.T), 0.01).T)   # same primal arithmetic
+    xs, As, Bs = ac.linearize(f32(x.T), f32(u.T), 0.01, layout="soa")
+    assert torch.equal(As.permute(2, 0, 1), A) and torch.equal(Bs.permute(2, 0, 1), B)
+    assert torch.equal(xs.T, xn)
+    # leading batch dims are kept: [windows, nodes, 13]
+    xw, Aw, Bw = ac.linearize(f32(x[:1000].reshape(20, 50, 13)), f32(u[:1000].reshape(20, 50, 7)), 0.01)
+    assert Aw.shape == (20, 50, 13, 13) and Bw.shape == (20, 50, 13, 7)
+    assert torch.equal(Aw.reshape(1000, 13, 13), A[:1000])
+
+
+def test_linearize_per_node_dt_and_stall_scaling(built):
+    from aircraft_b200 import Aircraft
+    ac = Aircraft.from_problem(com=TRIM_COM, device=DEV, physical_integration_substeps=1, stall_scaling=True)
+    orc = oracle_for(TRIM_COM, stall_scaling=True)
+    n = 2048
+    x, u = make_states(n, seed=43), make_controls(n, seed=43)
+    x[: n // 2, 3:6] *= np.array([0.6, 1.0, 2.0])         # push half of the nodes to high alpha
+    dt = np.random.default_rng(2).uniform(0.005, 0.02, n)
+    xn, A, B = ac.linearize(f32(x), f32(u), f32(dt))
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), t64(dt))
+    assert col_err(xn.cpu(), xo.numpy()) < PARITY_TOL
+    assert col_err(A.cpu(), Ao.numpy()) < PARITY_TOL
+    assert col_err(B.cpu(), Bo.numpy()) < PARITY_TOL
+
+
+def test_chain_rule_property(ac):
+    """Size-independent property: the Jacobian of two substeps of dt/2 equals the product of the
+    Jacobians of the two successive single steps (65536 nodes)."""
+    n = 65536
+    x, u = make_states(n, seed=44), make_controls(n, seed=44)
+    X, U = f32(x), f32(u)
+    x1, A1, B1 = ac.linearize(X, U, 0.01)
+    x2, A2, B2 = ac.linearize(x1, U, 0.01)
+    xx, AA, BB = ac.linearize(X, U, 0.02, substeps=2)
+    assert torch.equal(xx, x2)
+    Aprod = torch.bmm(A2, A1)
+    Bprod = torch.bmm(A2, B1) + B2
+    assert col_err(AA.cpu(), Aprod.cpu()) < PARITY_TOL
+    assert col_err(BB.cpu(), Bprod.cpu()) < PARITY_TOL
+
+
+def test_full_size_c2_determinism_and_sharding_invariance(ac):
+    """BASELINE config 2 (4096 x 200): bit-identical between runs and between a whole-batch launch
+    and two half-batch launches (what the multi-GPU sharding does); unit quaternions with
+    normalise."""
+    B, H = 4096, 200
+    x0, U = make_states(B, seed=45), make_control_sequences(B, H, seed=45, dtype=np.float32)
+    X0, UU = f32(x0.T), f32(U.transpose(1, 2, 0))
+    a = ac.rollout(X0, UU, 0.01, layout="soa", normalise=True, cost=True)
+    b = ac.rollout(X0, UU, 0.01, layout="soa", normalise=True, cost=True)
+    assert torch.equal(a.final, b.final) and torch.equal(a.cost, b.cost)
+    h = B // 2
+    lo = ac.rollout(X0[:, :h].contiguous(), UU[:, :, :h].contiguous(), 0.01, layout="soa", normalise=True, cost=True)
+    hi = ac.rollout(X0[:, h:].contiguous(), UU[:, :, h:].contiguous(), 0.01, layout="soa", normalise=True, cost=True)
+    assert torch.equal(torch.cat([lo.final, hi.final], 1), a.final)
+    assert torch.equal(torch.cat([lo.cost, hi.cost]), a.cost)
+    fin = torch.isfinite(a.final).all(0)
+    qn = (a.final[6:10, fin] ** 2).sum(0)
+    assert (qn - 1).abs().max() < 1e-6
+    m, i = ac.argmin(a.cost)
+    ref = torch.where(torch.isnan(a.cost), torch.full_like(a.cost, float("inf")), a.cost)
+    assert int(i) == int(ref.argmin())
+
+
+def test_sharded_sweep_single_process(ac):
+    """ShardedRollout without a process group == plain rollout + argmin, and hands back the
+    winner's trajectory."""
+    from aircraft_b200.sharding import ShardedRollout
+    B, H = 2000, 25
+    x0, U = make_states(B, seed=46), make_control_sequences(B, H, seed=46)
+    sr = ShardedRollout(ac)
+    res = sr.sweep(f32(x0.T), f32(U.transpose(1, 2, 0)), 0.01, B, layout="soa", gather_costs=True)
+    full = ac.rollout(f32(x0), f32(U), 0.01, return_trajectory=True, cost=True)
+    assert torch.equal(res.all_cost, full.cost)
+    j = int(torch.where(torch.isnan(full.cost), torch.full_like(full.cost, float("inf")), full.cost).argmin())
+    assert res.argmin == j and res.owner == 0
+    assert torch.equal(res.best_trajectory, full.trajectory[j])
+    assert torch.equal(res.best_controls, f32(U[j]))
