@@ -65,6 +65,7 @@ PROTOTYPES = {
     "airc_linearize": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                  _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "airc_measure_fp32_peak": (C.c_int, [_vp, _i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "airc_state_derivative_host": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
     "airc_state_update_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp]),
     "airc_rollout_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _i32, _vp, _vp,

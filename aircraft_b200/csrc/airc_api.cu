@@ -9,6 +9,7 @@
 #include "../../include/aircraft_b200.h"
 #include "airc_fuse.hpp"
 #include "airc_kernels.cuh"
+#include "airc_peak.cuh"
 
 using namespace airc;
 
@@ -214,6 +215,36 @@ int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_mi
   if (blocks > (long long)h->sm_count * 8) blocks = (long long)h->sm_count * 8;
   argmin_kernel<<<(unsigned)blocks, 256, 0, st>>>(cost, B, (unsigned long long*)out_idx);
   argmin_finish_kernel<<<1, 1, 0, st>>>((const unsigned long long*)out_idx, out_min, (long long*)out_idx);
+  return check_launch();
+}
+
+int airc_measure_fp32_peak(const AircHandle* h, int repeats, double* tflops, double* ms) {
+  if (!h || !tflops || repeats < 1) return fail(AIRC_EINVAL, "airc_measure_fp32_peak: bad argument%s", "");
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  float* d = nullptr;
+  CUDA_TRY(cudaMalloc(&d, 256));
+  cudaEvent_t e0, e1;
+  CUDA_TRY(cudaEventCreate(&e0));
+  CUDA_TRY(cudaEventCreate(&e1));
+  const int iters = 4096, blocks = h->sm_count * 8, threads = 256;
+  ffma_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 1e-4f);   // warm-up
+  double best = 1e30;
+  for (int r = 0; r < repeats; ++r) {
+    cudaEventRecord(e0);
+    ffma_peak_kernel<<<blocks, threads>>>(d, iters, 0.999f, 1e-4f);
+    cudaEventRecord(e1);
+    CUDA_TRY(cudaEventSynchronize(e1));
+    float t = 0.f;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (t < best) best = t;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(d);
+  const double flops = 2.0 * 64.0 * (double)iters * (double)blocks * (double)threads;
+  *tflops = flops / (best * 1e-3) * 1e-12;
+  if (ms) *ms = best;
   return check_launch();
 }
 

@@ -56,7 +56,7 @@ def global_argmin(local_min: torch.Tensor, local_global_idx: torch.Tensor,
 
 @dataclass
 class SweepResult:
-    min_cost: float
+    min_cost: Any                    # 0-dim tensor (no host sync is forced)
     argmin: int                      # global trajectory index
     owner: int                       # rank that held it
     best_trajectory: Any             # [H+1,13] on every rank
@@ -85,16 +85,24 @@ class ShardedRollout:
         given layout.  Runs the fused rollout+cost kernel, reduces (min, arg-min) on the device,
         exchanges it, and hands every rank the winner's trajectory (re-rolled by its owner: one
         extra single-trajectory launch instead of storing B trajectories)."""
+        res = self.aircraft.rollout(x0_local, U_local, dt, substeps=substeps, normalise=normalise,
+                                    layout=layout, return_final=False, cost=cost)
+        return self.finish_sweep(res.cost, x0_local, U_local, dt, total, layout=layout,
+                                 substeps=substeps, normalise=normalise, gather_costs=gather_costs)
+
+    def finish_sweep(self, cost_local, x0_local, U_local, dt: float, total: int, *, layout: str = "soa",
+                     substeps: Optional[int] = None, normalise: Optional[bool] = None,
+                     gather_costs: bool = False) -> SweepResult:
+        """Everything after the rollout kernel: device (min, arg-min) of this rank's costs, the
+        exchange, and the winner's trajectory on every rank."""
         ac = self.aircraft
         start, stop = self.local_range(total)
-        res = ac.rollout(x0_local, U_local, dt, substeps=substeps, normalise=normalise, layout=layout,
-                         return_final=False, cost=cost)
-        lmin, lidx = ac.argmin(res.cost)
+        lmin, lidx = ac.argmin(cost_local)
         gmin, gidx, owner = global_argmin(lmin, lidx + start, self.group)
         soa = layout == "soa"
         shared = U_local.ndim == 2
         H = U_local.shape[0] if (soa or shared) else U_local.shape[1]
-        dev = res.cost.device
+        dev = cost_local.device
         traj = torch.empty((H + 1, 13), dtype=torch.float32, device=dev)
         ctrl = torch.empty((H, 7), dtype=torch.float32, device=dev)
         if owner == self.rank:
@@ -108,13 +116,12 @@ class ShardedRollout:
             ctrl.copy_(ub)
         all_cost = None
         if self.world > 1:
-            dist.broadcast(traj, src=dist.get_global_rank(self.group, owner) if self.group else owner,
-                           group=self.group)
-            dist.broadcast(ctrl, src=dist.get_global_rank(self.group, owner) if self.group else owner,
-                           group=self.group)
+            src = dist.get_global_rank(self.group, owner) if self.group else owner
+            dist.broadcast(traj, src=src, group=self.group)
+            dist.broadcast(ctrl, src=src, group=self.group)
         if gather_costs:
-            all_cost = gather_varlen(res.cost, total, self.rank, self.world, self.group)
-        return SweepResult(float(gmin), gidx, owner, traj, ctrl, res.cost, all_cost)
+            all_cost = gather_varlen(cost_local, total, self.rank, self.world, self.group)
+        return SweepResult(gmin, gidx, owner, traj, ctrl, cost_local, all_cost)
 
 
 def gather_varlen(local: torch.Tensor, total: int, rank: int, world: int, group=None) -> torch.Tensor:

@@ -1,0 +1,477 @@
+#!/usr/bin/env python
+"""bench.py -- throughput of the AIrcraft hot path on B200 (driver contract: one JSON line).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload c4|c2]
+
+Metric (BASELINE.json): surrogate-RK4 state-steps/s (+ Jacobian evals/s) at 1/2/4/8 B200 next to
+the CPU path on the box's host cores.
+
+A "step" is one pass of the hot path over one batch of synthetic input:
+  workload c4 (default, every N): the per-GPU shard of BASELINE config 4, the sampling-MPC sweep
+      "1M control-sequence rollouts x horizon 200 sharded over 8 B200" = 125 000 rollouts x 200
+      RK4 steps per GPU from one shared initial state, fused rollout+cost kernel, device arg-min,
+      then (N>1) the NCCL exchange of (min, arg-min) and broadcast of the winner's trajectory.
+      Weak scaling: at N=8 the job is exactly config 4.  Inputs (700 MB of control sequences per
+      GPU) are larger than the 126 MB L2, so nothing is cached between timed iterations.
+  workload c2: BASELINE config 2, 4096 rollouts x 200 from trim states on each GPU (a latency
+      case: 128 warps on 592 SM sub-partitions); always reported under "extra" at N=1.
+  Jacobians: BASELINE config 3 (65 536 x 100 nodes) and config 5's per-GPU shard (51 200 nodes),
+      reported under "jacobian" / "extra".
+
+`--impl reference` times the CPU restatement of the reference path (oracle/cpu_ref.cpp, float64,
+OpenMP over all host cores; the reference's own CasADi evaluation cannot run on this box) on the
+same workload, each step a bounded sample of it.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+F_STEP = 3953          # algorithmic FLOPs per RK4 state-step (minimal form)
+B_JAC = 1172           # algorithmic HBM bytes per Jacobian eval: x,u in; x+, A, B out (FP32)
+F_JAC = 28000          # estimated algorithmic FLOPs per Jacobian eval
+DT = 0.01
+H_ROLL = 200
+C4_TOTAL, C4_GPUS = 1_000_000, 8
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # 74.4
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--workload", default="c4", choices=["c4", "c2"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the c2/c3/c5 side measurements")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU-baseline sample budget")
+    ap.add_argument("--per-gpu", type=int, default=0, help="override rollouts per GPU (debug)")
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi sampled every 200 ms DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def mark(self):
+        return time.time()
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self, windows):
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for t, line in self.rows:
+            if not any(a - 0.05 <= t <= b + 0.25 for a, b in windows):
+                continue
+            f = [c.strip() for c in line.split(",")]
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except Exception:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)),
+                "power_w_max": float(max(pw)), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- CPU legs
+def _cpu_ref(threads: int = 0):
+    """The float64 C++ restatement (oracle/cpu_ref.cpp).  bench.py may execute oracle/ only here:
+    the cpu_baseline leg and the --impl reference arm."""
+    from aircraft_b200.config import AircraftConfiguration, TRIM_COM
+    from aircraft_b200.params import load_nn_blob, make_params
+    from oracle.cpu_ref import CpuRef
+    p = make_params(AircraftConfiguration.from_json(), com=TRIM_COM)
+    return CpuRef(p, load_nn_blob(), threads=threads)
+
+
+def _cpu_sample_inputs(n: int, horizon: int):
+    from aircraft_b200.workloads import make_control_sequences, make_states
+    x0 = np.repeat(make_states(1, seed=4, level=True), n, axis=0)
+    U = make_control_sequences(n, horizon, seed=4)
+    return x0, U
+
+
+def cpu_rollout_rate(ref, seconds: float, horizon: int = H_ROLL):
+    """state-steps/s of the CPU restatement on a bounded sample of the c4/c2 workload: calibrate
+    on one trajectory per thread, then size the sample to ~`seconds` of work."""
+    n0 = max(ref.threads, 1)
+    x0, U = _cpu_sample_inputs(n0, horizon)
+    t = time.perf_counter(); ref.rollout(x0, U, DT, normalise=True, trajectory=False); t0 = time.perf_counter() - t
+    per_traj = max(t0, 1e-4)      # one trajectory per thread in parallel
+    reps = int(max(1, min(4096, seconds / per_traj)))
+    n = n0 * reps
+    x0, U = _cpu_sample_inputs(n, horizon)
+    t = time.perf_counter(); ref.rollout(x0, U, DT, normalise=True, trajectory=False); el = time.perf_counter() - t
+    return n * horizon / el, n, el
+
+
+def cpu_jacobian_rate(ref, seconds: float):
+    from aircraft_b200.workloads import make_controls, make_states
+    n0 = max(ref.threads, 1) * 16
+    x, u = make_states(n0, seed=5, perturb_norm=1e-3), make_controls(n0, seed=5)
+    t = time.perf_counter(); ref.linearize(x, u, DT, normalise=True); t0 = max(time.perf_counter() - t, 1e-4)
+    n = int(max(n0, min(2_000_000, n0 * seconds / t0)))
+    x, u = make_states(n, seed=5, perturb_norm=1e-3), make_controls(n, seed=5)
+    t = time.perf_counter(); ref.linearize(x, u, DT, normalise=True); el = time.perf_counter() - t
+    return n / el, n, el
+
+
+def run_reference(args):
+    """--impl reference: the CPU restatement of the reference path, all host threads, same metric
+    and config; each step is a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    ref = _cpu_ref()
+    per_gpu = args.per_gpu or (C4_TOTAL // C4_GPUS if args.workload == "c4" else 4096)
+    # size one step to ~2 s so that K+W steps end within a few minutes
+    rate, _, _ = cpu_rollout_rate(ref, 1.0)
+    n = int(max(ref.threads, min(per_gpu, rate * 2.0 / H_ROLL)))
+    x0, U = _cpu_sample_inputs(n, H_ROLL)
+    for _ in range(args.warmup):
+        ref.rollout(x0, U, DT, normalise=True, trajectory=False)
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        ref.rollout(x0, U, DT, normalise=True, trajectory=False)
+    el = time.perf_counter() - t
+    value = n * H_ROLL * args.steps / el
+    jrate, jn, _ = cpu_jacobian_rate(ref, 3.0)
+    line = {
+        "impl": "reference", "metric": "surrogate RK4 state-steps/s", "value": value,
+        "unit": "state-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": el / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": workload_config(args.workload, per_gpu, args.gpus),
+        "cpu_baseline": {"value": value, "unit": "state-steps/s", "cores": ref.threads, "kind": "port",
+                         "sample": f"{n} rollouts x {H_ROLL} steps per step (of {per_gpu} per GPU), "
+                                   "oracle/cpu_ref.cpp float64 OpenMP; the reference's CasADi VM cannot run here"},
+        "jacobian": {"value": jrate, "unit": "jacobian-evals/s", "sample": f"{jn} nodes, 20-direction forward mode"},
+        "e2e": {"value": value, "unit": "state-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(workload: str, per_gpu: int, gpus: int):
+    if workload == "c4":
+        name = (f"BASELINE config 4 shard: sampling-MPC sweep, {per_gpu} control-sequence rollouts x "
+                f"horizon {H_ROLL} per GPU from one shared state ({per_gpu * gpus} total; "
+                f"1M total at 8 GPUs), fused cost + arg-min + best-trajectory exchange")
+    else:
+        name = f"BASELINE config 2: {per_gpu} rollouts x horizon {H_ROLL} from trim states per GPU"
+    return {"workload": name, "rollouts_per_gpu": per_gpu, "horizon": H_ROLL, "dt": DT,
+            "substeps": 1, "normalise": True, "layout": "soa", "parallelism": f"dp{gpus}",
+            "l2_policy": "inputs larger than L2 (700 MB of control sequences per GPU per step)"
+            if workload == "c4" else "L2 flushed between timed iterations (256 MB write)"}
+
+
+# ----------------------------------------------------------------------------- GPU legs
+def device_control_sequences(torch, n: int, horizon: int, seed: int, device):
+    """[H,7,n] FP32 random-walk control sequences generated on the device (synthetic data; same
+    distribution family as workloads.make_control_sequences, clipped to the actuator limits)."""
+    g = torch.Generator(device=device).manual_seed(20250101 + seed)
+    U = torch.empty((horizon, 7, n), dtype=torch.float32, device=device)
+    lo = torch.tensor([-5.0, -5.0, -5.0, 0.0, 0.0, 0.0, 0.0], device=device).view(7, 1)
+    hi = torch.tensor([5.0, 5.0, 5.0, 0.0, 0.0, 0.0, 1.0], device=device).view(7, 1)
+    sg = torch.tensor([0.25, 0.25, 0.25, 0.0, 0.0, 0.0, 0.025], device=device).view(7, 1)
+    u = lo + (hi - lo) * torch.rand((7, n), generator=g, device=device)
+    for k in range(horizon):
+        U[k] = u
+        u = torch.minimum(torch.maximum(u + sg * torch.randn((7, n), generator=g, device=device), lo), hi)
+    return U
+
+
+def time_launches(torch, fn, steps: int, warmup: int, flush=None):
+    """Average device time of fn() in ms: CUDA events on the current stream around every call,
+    optional L2 flush before each."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(steps):
+        if flush is not None:
+            flush.add_(1.0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    return sum(a.elapsed_time(b) for a, b in evs) / steps
+
+
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+    from aircraft_b200 import Aircraft
+    from aircraft_b200.config import TRIM_COM
+    from aircraft_b200.sharding import ShardedRollout
+    from aircraft_b200.workloads import make_states, trim_states
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; aircraft_b200 has no CPU path (use --impl reference)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if world != args.gpus and rank == 0:
+        print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
+
+    ac = Aircraft.from_problem(com=TRIM_COM, device=local, physical_integration_substeps=1, normalise=True)
+    sr = ShardedRollout(ac)
+    per_gpu = args.per_gpu or (C4_TOTAL // C4_GPUS if args.workload == "c4" else 4096)
+    total = per_gpu * world
+    H, K, W = H_ROLL, args.steps, max(args.warmup, 3)
+    launches = 0
+
+    # ---- inputs resident in HBM before the timed region
+    if args.workload == "c4":
+        x1 = make_states(1, seed=4, level=True)
+        x0 = torch.tensor(x1.T, dtype=torch.float32, device=dev).expand(13, per_gpu).contiguous()
+    else:
+        xs, _ = trim_states(ac, per_gpu, seed=rank)
+        x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
+    U = device_control_sequences(torch, per_gpu, H, seed=100 + rank, device=dev)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev) if args.workload == "c2" else None
+    torch.cuda.synchronize()
+
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    windows = []
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- `value`: device-resident inputs, whole step = fused rollout+cost, arg-min, exchange
+    roll_events = []
+
+    def step(record: bool):
+        if flush is not None:
+            flush.add_(1.0)
+        if record:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        res = ac.rollout(x0, U, DT, layout="soa", return_final=False, cost=True)
+        if record:
+            e1.record(); roll_events.append((e0, e1))
+        return sr.finish_sweep(res.cost, x0, U, DT, total, layout="soa")
+
+    for _ in range(W):
+        out = step(False)
+    barrier()
+    t_mark = clocks.mark()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(K):
+        out = step(True)
+    s1.record()
+    barrier()
+    windows.append((t_mark, clocks.mark()))
+    ms_total = s0.elapsed_time(s1)
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / K
+    value = total * H / (ms_step * 1e-3)
+    launches += K * (1 + 2 + 1)      # rollout, argmin (+finish), winner re-roll
+    ms_roll = sum(a.elapsed_time(b) for a, b in roll_events) / K
+    roll_tflops = per_gpu * H * F_STEP / (ms_roll * 1e-3) / 1e12
+
+    # ---- FP32 FMA peak of this device, measured now (no vendor number in MEASURED_PEAKS.json)
+    import ctypes as C
+    tf, ms = C.c_double(), C.c_double()
+    ac._lib.airc_measure_fp32_peak(ac.handle, 5, C.byref(tf), C.byref(ms))
+    fp32_peak = float(tf.value)
+
+    # ---- `e2e`: the same step through the host-buffer C ABI (airc_rollout_host): pinned host
+    #      inputs copied H2D, kernel, per-trajectory costs copied D2H, arg-min on the host
+    x0_h = torch.empty((13, per_gpu), dtype=torch.float32).pin_memory()
+    U_h = torch.empty((H, 7, per_gpu), dtype=torch.float32).pin_memory()
+    x0_h.copy_(x0); U_h.copy_(U)
+    x0_np, U_np = x0_h.numpy(), U_h.numpy()
+    h2d = x0_np.nbytes + U_np.nbytes
+    d2h = 4 * per_gpu
+    Ke = max(3, min(K, 10))
+
+    def e2e_step():
+        r = ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
+        return int(np.nanargmin(r.cost))
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t_mark = clocks.mark()
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        best = e2e_step()
+    torch.cuda.synchronize()
+    el = time.perf_counter() - t0
+    windows.append((t_mark, clocks.mark()))
+    if world > 1:
+        t = torch.tensor([el], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+    e2e_value = total * H * Ke / el
+    del x0_h, U_h
+
+    line = {
+        "metric": "surrogate RK4 state-steps/s", "value": value, "unit": "state-steps/s",
+        "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args.workload, per_gpu, world),
+        "e2e": {"value": e2e_value, "unit": "state-steps/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": Ke,
+                "path": "airc_rollout_host (C ABI, pinned host buffers) + host arg-min"},
+        "gpu_launches": launches,
+        "roofline": {"kernel": "rollout_kernel<cost>", "bound": "fp32", "achieved": roll_tflops,
+                     "peak": fp32_peak, "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak,
+                     "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); "
+                                    "MEASURED_PEAKS.json has no FP32 CUDA-core entry",
+                     "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": roll_tflops / FP32_NOMINAL_TFLOPS,
+                     "flops_per_state_step": F_STEP, "state_steps_per_launch": per_gpu * H,
+                     "kernel_ms": ms_roll, "kernel_share_of_step": ms_roll / ms_step,
+                     "traffic": None},
+    }
+
+    # ---- side measurements on rank 0 / every rank (no collectives inside)
+    extra = {}
+    if not args.no_extras:
+        extra.update(side_measurements(torch, ac, dev, rank, args))
+        if "c3" in extra:
+            line["jacobian"] = extra.pop("c3")
+    if rank == 0 and world == 1:
+        ref = _cpu_ref()
+        rate, n, sec = cpu_rollout_rate(ref, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": rate, "unit": "state-steps/s", "cores": ref.threads, "kind": "port",
+                                "sample": f"{n} rollouts x {H} steps ({sec:.1f} s) of the same workload, "
+                                          "oracle/cpu_ref.cpp float64 OpenMP (CasADi cannot run on this box)"}
+        if "jacobian" in line:
+            jr, jn, js = cpu_jacobian_rate(ref, 4.0)
+            line["jacobian"]["cpu_baseline"] = {"value": jr, "unit": "jacobian-evals/s", "cores": ref.threads,
+                                                "kind": "port", "sample": f"{jn} nodes ({js:.1f} s)"}
+    if extra:
+        line["extra"] = extra
+    if rank == 0:
+        clocks.stop()
+        line["clocks"] = clocks.summary(windows)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return json.load(open(p)), "measured (MEASURED_PEAKS.json)"
+        except Exception:
+            pass
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
+
+
+def side_measurements(torch, ac, dev, rank, args):
+    """The other BASELINE configs, device-timed with CUDA events (per GPU; no collectives)."""
+    from aircraft_b200.workloads import make_controls, make_states, trim_states
+    out = {}
+    peaks, peak_src = measured_peaks()
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)   # 256 MB > 126 MB L2
+    K = max(5, min(args.steps, 20))
+
+    # config 2: 4096 rollouts x 200 from trim states (latency case)
+    if args.workload != "c2":
+        xs, us = trim_states(ac, 4096, seed=rank)
+        x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
+        U = device_control_sequences(torch, 4096, H_ROLL, seed=200 + rank, device=dev)
+        ms = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True), K, 3, flush)
+        out["c2"] = {"workload": "BASELINE config 2: 4096 rollouts x horizon 200 from trim states, 1 GPU",
+                     "value": 4096 * H_ROLL / (ms * 1e-3), "unit": "state-steps/s", "ms_per_launch": ms,
+                     "tflops": 4096 * H_ROLL * F_STEP / (ms * 1e-3) / 1e12, "l2": "flushed between launches"}
+
+    # config 3: 65 536 x 100 nodes, (x+, A, B) at every node, SoA outputs (7.7 GB written)
+    n_unique, rep = 655_360, 10
+    x = torch.tensor(make_states(n_unique, seed=300 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev)
+    u = torch.tensor(make_controls(n_unique, seed=300 + rank).T, dtype=torch.float32, device=dev)
+    x, u = x.repeat(1, rep).contiguous(), u.repeat(1, rep).contiguous()
+    n = x.shape[1]
+    ms = time_launches(torch, lambda: ac.linearize(x, u, DT, layout="soa"), K, 3, None)
+    gbs = n * B_JAC / (ms * 1e-3) / 1e9
+    out["c3"] = {"workload": "BASELINE config 3: 65 536 x 100 multiple-shooting nodes, dPhi/dx and dPhi/du at every node",
+                 "value": n / (ms * 1e-3), "unit": "jacobian-evals/s", "nodes": n, "ms_per_launch": ms,
+                 "l2": "outputs (7.7 GB) larger than L2",
+                 "roofline": {"kernel": "linearize_kernel", "bound": "hbm", "achieved": gbs,
+                              "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
+                              "peak_source": peak_src, "bytes_per_eval": B_JAC, "traffic": None,
+                              "tflops_est": n * F_JAC / (ms * 1e-3) / 1e12}}
+    del x, u
+
+    # config 5 shard: 8192 windows x 50 nodes over 8 GPUs = 51 200 nodes per GPU (latency-bound)
+    n5 = 8192 * 50 // 8
+    x = torch.tensor(make_states(n5, seed=500 + rank, perturb_norm=1e-3), dtype=torch.float32, device=dev)
+    u = torch.tensor(make_controls(n5, seed=500 + rank), dtype=torch.float32, device=dev)
+    xw, uw = x.view(-1, 50, 13), u.view(-1, 50, 7)
+    ms = time_launches(torch, lambda: ac.linearize(xw, uw, DT), K, 3, flush)
+    out["c5_shard"] = {"workload": "BASELINE config 5 shard: 1024 windows x 50 nodes per GPU, A[.,13,13], B[.,13,7] (AoS)",
+                       "value": n5 / (ms * 1e-3), "unit": "jacobian-evals/s", "ms_per_launch": ms,
+                       "l2": "flushed between launches"}
+    return out
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_native(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -150,6 +150,11 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
 int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
                 int64_t* out_idx, void* stream);
 
+/* Measures the device's FP32 FFMA throughput (independent fused multiply-adds, all SMs, best of
+ * `repeats` launches, CUDA events): the roofline denominator of the rollout kernel, which no
+ * vendor library reports.  Synchronises.  ms (optional) receives the best launch time. */
+int airc_measure_fp32_peak(const AircHandle* h, int repeats, double* tflops, double* ms);
+
 /* Convenience for FFI callers that hold HOST buffers (the cgo/ctypes style binding a maintainer
  * of the reference would use from numpy): allocates device scratch, copies in, runs, copies out,
  * synchronises.  Same semantics as the device-pointer versions. */
