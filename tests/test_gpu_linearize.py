@@ -44,7 +44,8 @@ def test_linearize_structure_and_layouts(ac):
     eye = torch.eye(13, device=DEV)[:, :3]
     assert torch.equal(A[:, :, :3], eye.expand(n, 13, 3))      # dPhi/dp = [I;0] exactly
     assert torch.count_nonzero(B[:, :, 3:6]) == 0              # thrust is inert (aircraft.py:320)
-    assert torch.equal(xn, ac.state_update(f32(x.T), f32(u.T), 0.01).T)   # same primal arithmetic
+    # same primal formulas; the two kernels are compiled separately, so FMA contraction may differ in the last ulp
+    assert col_err(xn.cpu(), ac.state_update(f32(x.T), f32(u.T), 0.01).T.cpu()) < 1e-6
     xs, As, Bs = ac.linearize(f32(x.T), f32(u.T), 0.01, layout="soa")
     assert torch.equal(As.permute(2, 0, 1), A) and torch.equal(Bs.permute(2, 0, 1), B)
     assert torch.equal(xs.T, xn)
@@ -78,7 +79,7 @@ def test_chain_rule_property(ac):
     x1, A1, B1 = ac.linearize(X, U, 0.01)
     x2, A2, B2 = ac.linearize(x1, U, 0.01)
     xx, AA, BB = ac.linearize(X, U, 0.02, substeps=2)
-    assert torch.equal(xx, x2)
+    assert col_err(xx.cpu(), x2.cpu()) < 1e-6
     Aprod = torch.bmm(A2, A1)
     Bprod = torch.bmm(A2, B1) + B2
     assert col_err(AA.cpu(), Aprod.cpu()) < PARITY_TOL
