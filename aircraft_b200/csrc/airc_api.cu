@@ -141,10 +141,11 @@ int airc_state_update(const AircHandle* h, const float* x, const float* u, float
 int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt, int64_t B,
                  int H, int substeps, uint32_t flags, int layout, float* X, float* x_final,
                  float* cost, const AircCostParams* cp, void* stream) {
-  if (!h || !x0 || (!U && H > 0) || B < 0 || H < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
+  if (!h || B < 0 || H < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U)) || (cost && !cp))
     return fail(AIRC_EINVAL, "airc_rollout: bad argument%s", "");
-  if (B == 0) return AIRC_OK;
+  if (B == 0) return AIRC_OK;   // empty batch: nothing to read, so NULL data pointers are fine
+  if (!x0 || (!U && H > 0)) return fail(AIRC_EINVAL, "airc_rollout: NULL x0 or U%s", "");
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   RolloutArgs a;
@@ -308,8 +309,9 @@ int airc_state_update_host(AircHandle* h, const float* x, const float* u, float 
 int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, int64_t B, int H,
                       int substeps, uint32_t flags, int layout, float* X, float* x_final,
                       float* cost, const AircCostParams* cp) {
-  if (!h || !x0 || (!U && H > 0) || B < 0 || H < 0) return fail(AIRC_EINVAL, "airc_rollout_host: bad argument%s", "");
+  if (!h || B < 0 || H < 0) return fail(AIRC_EINVAL, "airc_rollout_host: bad argument%s", "");
   if (B == 0) return AIRC_OK;
+  if (!x0 || (!U && H > 0)) return fail(AIRC_EINVAL, "airc_rollout_host: NULL x0 or U%s", "");
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   const size_t nU = (flags & AIRC_FLAG_SHARED_U) ? (size_t)7 * H : (size_t)7 * H * B;

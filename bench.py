@@ -213,15 +213,16 @@ def device_control_sequences(torch, n: int, horizon: int, seed: int, device):
     """[H,7,n] FP32 random-walk control sequences generated on the device (synthetic data; same
     distribution family as workloads.make_control_sequences, clipped to the actuator limits)."""
     g = torch.Generator(device=device).manual_seed(20250101 + seed)
-    U = torch.empty((horizon, 7, n), dtype=torch.float32, device=device)
-    lo = torch.tensor([-5.0, -5.0, -5.0, 0.0, 0.0, 0.0, 0.0], device=device).view(7, 1)
-    hi = torch.tensor([5.0, 5.0, 5.0, 0.0, 0.0, 0.0, 1.0], device=device).view(7, 1)
-    sg = torch.tensor([0.25, 0.25, 0.25, 0.0, 0.0, 0.0, 0.025], device=device).view(7, 1)
-    u = lo + (hi - lo) * torch.rand((7, n), generator=g, device=device)
-    for k in range(horizon):
-        U[k] = u
-        u = torch.minimum(torch.maximum(u + sg * torch.randn((7, n), generator=g, device=device), lo), hi)
-    return U
+    lo = torch.tensor([-5.0, -5.0, -5.0, 0.0, 0.0, 0.0, 0.0], device=device).view(1, 7, 1)
+    hi = torch.tensor([5.0, 5.0, 5.0, 0.0, 0.0, 0.0, 1.0], device=device).view(1, 7, 1)
+    sg = torch.tensor([0.25, 0.25, 0.25, 0.0, 0.0, 0.0, 0.025], device=device).view(1, 7, 1)
+    # a handful of launches (not 4 per step of the horizon), so that an ncu launch list of the
+    # bench command is dominated by the product's kernels
+    U = torch.randn((horizon, 7, n), generator=g, device=device, dtype=torch.float32)
+    U.mul_(sg)
+    U[0] = (lo + (hi - lo) * torch.rand((1, 7, n), generator=g, device=device))[0]
+    torch.cumsum(U, dim=0, out=U)
+    return torch.minimum(torch.maximum(U, lo), hi, out=U)
 
 
 def time_launches(torch, fn, steps: int, warmup: int, flush=None):
