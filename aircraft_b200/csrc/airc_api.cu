@@ -168,7 +168,7 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
   a.dt = dt; a.B = B; a.H = H; a.substeps = substeps;
   a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
   // small batches: one warp per block so that every SM gets work
-  const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : 128);
+  const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : AIRC_ROLLOUT_BS);
   const unsigned grid = (unsigned)((B + bs - 1) / bs);
   cudaStream_t st = (cudaStream_t)stream;
   if (cost && X) rollout_kernel<true, true><<<grid, bs, 0, st>>>(h->dc, a);

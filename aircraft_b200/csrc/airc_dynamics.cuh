@@ -24,12 +24,18 @@ constexpr int NH = 32;  // hidden units after folding Linear(5,16).Linear(16,32)
 //   C_k  = c0_k + sum_j Wo[k][j] r_j,   r_j = 1/(1+2^h_j)
 //   Wo   = -2 sigma_out W3,  c0 = sigma_out (b3 + W3.1) + mu_out
 //   dC_k/din_i = sum_j Wo[k][j] g_j A[j][i],  g_j = -ln2 r_j (1-r_j)
-struct FusedNet {
-  float Ax[NH][3];
-  float Au[NH][2];
-  float a0[NH];
-  float Wo[6][NH];
+// Hidden units are stored in PAIRS (2p, 2p+1) with the two weights of every input adjacent, so
+// that one LDCU.128 delivers two packed FFMA2 multiplicands.
+struct alignas(16) HidPair {
+  float a0[2];
+  float Au[2][2];   // [aileron|elevator][unit in pair]
+  float Ax[3][2];   // [qbar|alpha|beta][unit in pair]
+};
+struct alignas(16) FusedNet {
+  HidPair hid[NH / 2];
+  float Wo[6][NH];  // (Wo[k][2p], Wo[k][2p+1]) is the packed multiplicand of the output layer
   float c0[6];
+  float pad_[2];
 };
 
 // Everything a kernel needs, passed BY VALUE as a __grid_constant__ kernel parameter so that
@@ -113,52 +119,52 @@ AIRC_HD void rot_matrix_tangent(const float q[4], const float dq[4], float dM[9]
   dM[7] = 2.0f * (dyz + dwx);
 }
 
-// hidden layer + output layer.  cu[j] = a0_j + Au[j].(da,de) is hoisted by the caller when
-// the control is constant over several evaluations (all four RK4 stages and all substeps).
+// hidden layer + output layer, two hidden units per packed instruction.
 template <bool WITH_JAC>
 AIRC_HD void surrogate(const FusedNet& net, float qbar, float alpha, float beta, const Ctl& c,
                        float C[6], float J[6][5]) {
+  F2 acc[6];
+  F2 Jacc[WITH_JAC ? 6 : 1][WITH_JAC ? 5 : 1];
 #pragma unroll
   for (int k = 0; k < 6; ++k) {
-    C[k] = net.c0[k];
+    acc[k] = F2{net.c0[k], 0.0f};
     if (WITH_JAC) {
 #pragma unroll
-      for (int i = 0; i < 5; ++i) J[k][i] = 0.0f;
+      for (int i = 0; i < 5; ++i) Jacc[k][i] = F2{0.0f, 0.0f};
+    }
+  }
+  const F2 da = bc2(c.da), de = bc2(c.de), qb = bc2(qbar), al = bc2(alpha), be = bc2(beta);
+#pragma unroll
+  for (int p = 0; p < NH / 2; ++p) {
+    const HidPair& w = net.hid[p];
+    F2 h = F2{w.a0[0], w.a0[1]};
+    h = fma2(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+    h = fma2(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+    h = fma2(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+    h = fma2(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+    h = fma2(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+    const F2 r = sigm2_x2(h);   // AIRC_SIGM_MODE selects the variant (airc_math.cuh)
+#pragma unroll
+    for (int k = 0; k < 6; ++k) acc[k] = fma2(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, r, acc[k]);
+    if (WITH_JAC) {
+      // g_j = d r_j / d h_j = -ln2 r (1 - r)
+      const F2 g = mul2(mul2(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        const F2 wi = (i < 3) ? F2{w.Ax[i][0], w.Ax[i][1]} : F2{w.Au[i - 3][0], w.Au[i - 3][1]};
+        const F2 gw = mul2(g, wi);
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          Jacc[k][i] = fma2(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, gw, Jacc[k][i]);
+      }
     }
   }
 #pragma unroll
-  for (int j = 0; j < NH; j += 2) {
-    float h0 = net.a0[j], h1 = net.a0[j + 1];
-    h0 = fmaf(net.Au[j][0], c.da, h0);
-    h1 = fmaf(net.Au[j + 1][0], c.da, h1);
-    h0 = fmaf(net.Au[j][1], c.de, h0);
-    h1 = fmaf(net.Au[j + 1][1], c.de, h1);
-    h0 = fmaf(net.Ax[j][0], qbar, h0);
-    h1 = fmaf(net.Ax[j + 1][0], qbar, h1);
-    h0 = fmaf(net.Ax[j][1], alpha, h0);
-    h1 = fmaf(net.Ax[j + 1][1], alpha, h1);
-    h0 = fmaf(net.Ax[j][2], beta, h0);
-    h1 = fmaf(net.Ax[j + 1][2], beta, h1);
-    float r0, r1;
-    sigm2_pair(h0, h1, r0, r1);
-#pragma unroll
-    for (int k = 0; k < 6; ++k) {
-      C[k] = fmaf(net.Wo[k][j], r0, C[k]);
-      C[k] = fmaf(net.Wo[k][j + 1], r1, C[k]);
-    }
+  for (int k = 0; k < 6; ++k) {
+    C[k] = acc[k].lo + acc[k].hi;
     if (WITH_JAC) {
-      const float g0 = -0.69314718056f * r0 * (1.0f - r0);
-      const float g1 = -0.69314718056f * r1 * (1.0f - r1);
 #pragma unroll
-      for (int i = 0; i < 5; ++i) {
-        const float w0 = g0 * (i < 3 ? net.Ax[j][i] : net.Au[j][i - 3]);
-        const float w1 = g1 * (i < 3 ? net.Ax[j + 1][i] : net.Au[j + 1][i - 3]);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) {
-          J[k][i] = fmaf(net.Wo[k][j], w0, J[k][i]);
-          J[k][i] = fmaf(net.Wo[k][j + 1], w1, J[k][i]);
-        }
-      }
+      for (int i = 0; i < 5; ++i) J[k][i] = Jacc[k][i].lo + Jacc[k][i].hi;
     }
   }
 }

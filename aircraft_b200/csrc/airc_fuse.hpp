@@ -32,11 +32,11 @@ inline void fuse_network(const AircNNBlob& nn, FusedNet& out) {
       const double wsc = W21[j][i] / (double)nn.input_std[i];
       a0 -= wsc * (double)nn.input_mean[i];
       if (i < 3)
-        out.Ax[j][i] = (float)(kappa * wsc);
+        out.hid[j / 2].Ax[i][j % 2] = (float)(kappa * wsc);
       else
-        out.Au[j][i - 3] = (float)(kappa * wsc);
+        out.hid[j / 2].Au[i - 3][j % 2] = (float)(kappa * wsc);
     }
-    out.a0[j] = (float)(kappa * a0);
+    out.hid[j / 2].a0[j % 2] = (float)(kappa * a0);
   }
   for (int k = 0; k < 6; ++k) {
     double c0 = nn.b3[k];

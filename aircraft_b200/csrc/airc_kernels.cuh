@@ -139,8 +139,16 @@ AIRC_D float body_speed2(const DevConst& P, const State& s) {
   return acc;
 }
 
+// 4 blocks of 128 threads per SM = 128 registers per thread, no spills; 5 or 6 blocks per SM
+// (96 / 80 registers) spill and are 9-18 % slower (profiles/r1_variants.txt).
+#ifndef AIRC_ROLLOUT_MINBLOCKS
+#define AIRC_ROLLOUT_MINBLOCKS 4
+#endif
+#ifndef AIRC_ROLLOUT_BS
+#define AIRC_ROLLOUT_BS 128
+#endif
 template <bool COST, bool TRAJ>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(AIRC_ROLLOUT_BS, AIRC_ROLLOUT_MINBLOCKS)
 rollout_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= a.B) return;

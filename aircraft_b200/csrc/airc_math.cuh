@@ -66,6 +66,58 @@ AIRC_HD void sqrt_rsqrt(float x, float& s, float& rs) {
   rs = fmaf(r, e, r);
 }
 
+// ---------------------------------------------------------------- packed FP32x2 (Blackwell FFMA2)
+// sm_100 adds fma/add/mul.rn.f32x2 on 64-bit register pairs (SASS FFMA2/FADD2/FMUL2): the same
+// FMA-lane throughput as two FFMA but ONE issue slot, and the multiplier may be a pair of uniform
+// registers (LDCU.128 feeds two FFMA2 = four weights).  Measured on B200 (profiles/
+// r1_pipe_probe.txt): FFMA2 with a uniform operand 123 FMA-lanes/clk/SM vs 115 for FFMA, so the
+// gain is purely in issue slots -- which is what bounds the rollout kernel.
+struct F2 {
+  float lo, hi;
+};
+
+#if defined(__CUDA_ARCH__)
+AIRC_D unsigned long long f2_pack(const F2& a) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a.lo), "f"(a.hi));
+  return r;
+}
+AIRC_D F2 f2_unpack(unsigned long long v) {
+  F2 a;
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(a.lo), "=f"(a.hi) : "l"(v));
+  return a;
+}
+#endif
+
+AIRC_HD F2 fma2(const F2& a, const F2& b, const F2& c) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)), "l"(f2_pack(c)));
+  return f2_unpack(d);
+#else
+  return F2{fmaf(a.lo, b.lo, c.lo), fmaf(a.hi, b.hi, c.hi)};
+#endif
+}
+AIRC_HD F2 add2(const F2& a, const F2& b) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+  return f2_unpack(d);
+#else
+  return F2{a.lo + b.lo, a.hi + b.hi};
+#endif
+}
+AIRC_HD F2 mul2(const F2& a, const F2& b) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+  return f2_unpack(d);
+#else
+  return F2{a.lo * b.lo, a.hi * b.hi};
+#endif
+}
+AIRC_HD F2 bc2(float a) { return F2{a, a}; }
+
 // ---------------------------------------------------------------- logistic in base 2
 // The surrogate's tanh is evaluated as tanh(a) = 1 - 2 r, r = 1/(1 + 2^h), h = 2*log2(e)*a.
 // The factor 2*log2(e) is folded into the first-layer weights and the affine map t -> r into
@@ -77,6 +129,28 @@ AIRC_HD void sqrt_rsqrt(float x, float& s, float& rs) {
 AIRC_HD float sigm2(float h) {
   float e = fast_ex2(fminf(h, AIRC_H_CLAMP));
   return fast_rcp(1.0f + e);
+}
+
+// Logistic pair without a clamp: 2^h -> +inf gives 1+inf = inf and rcp(inf) = 0 (tanh = +1);
+// 2^h -> 0 (ftz) gives r = 1 (tanh = -1); NaN propagates.  2 issue slots + 2 MUFU per unit.
+// MUFU runs at 4 lanes/clk/SMSP (8 cycles per warp instruction, measured), i.e. 16 XU-cycles per
+// hidden unit here against 12 for the shared-reciprocal form below, which in turn costs 2 more
+// issue slots per unit (clamp + 1.5 multiplies); the kernel is issue-bound, so this form wins.
+// A/B on B200 (profiles/r1_variants.txt): mode 1 (shared reciprocal) 2.72 ms vs mode 0 (no clamp,
+// two reciprocals) 2.78 ms per 25M state-steps: the XU pipe (47 % busy in mode 1) matters more than
+// the two extra issue slots.
+#ifndef AIRC_SIGM_MODE
+#define AIRC_SIGM_MODE 1
+#endif
+AIRC_HD F2 sigm2_x2(const F2& h) {
+#if AIRC_SIGM_MODE == 0
+  const F2 d = add2(F2{fast_ex2(h.lo), fast_ex2(h.hi)}, F2{1.0f, 1.0f});
+  return F2{fast_rcp(d.lo), fast_rcp(d.hi)};
+#else  // shared reciprocal (3 MUFU per pair), needs the clamp so that d0*d1 stays finite
+  const F2 d = add2(F2{fast_ex2(fminf(h.lo, 40.0f)), fast_ex2(fminf(h.hi, 40.0f))}, F2{1.0f, 1.0f});
+  const float inv = fast_rcp(d.lo * d.hi);
+  return F2{d.hi * inv, d.lo * inv};
+#endif
 }
 
 // two logistic values with ONE reciprocal (Montgomery's trick): 3 MUFU instead of 4.

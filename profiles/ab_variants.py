@@ -1,0 +1,32 @@
+"""A/B timing of library build variants (build/variants/*.so) on the c4-shard rollout.
+Each variant runs in its own process (AIRC_LIB selects the .so).  Usage on the GPU box:
+  python profiles/ab_variants.py [names...]"""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+CHILD = r'''
+import sys, torch
+sys.path.insert(0, %r)
+from aircraft_b200 import Aircraft
+from aircraft_b200.config import TRIM_COM
+from aircraft_b200.workloads import make_states
+from bench import device_control_sequences, time_launches
+B = int(sys.argv[1])
+dev = torch.device("cuda", 0)
+ac = Aircraft.from_problem(com=TRIM_COM, device=0, physical_integration_substeps=1, normalise=True)
+x0 = torch.tensor(make_states(1, seed=4, level=True).T, dtype=torch.float32, device=dev).expand(13, B).contiguous()
+U = device_control_sequences(torch, B, 200, seed=100, device=dev)
+ms = time_launches(torch, lambda: ac.rollout(x0, U, 0.01, layout="soa", return_final=False, cost=True), 10, 3)
+r = ac.rollout(x0, U, 0.01, layout="soa", return_final=False, cost=True)
+print("%%.4f ms  %%.3e steps/s  %%.2f TFLOP/s  checksum %%.6e" %% (ms, B*200/ms*1e3, B*200*3953/ms*1e3/1e12, float(r.cost.nan_to_num(0).double().sum())))
+''' % str(ROOT)
+
+names = sys.argv[1:] or sorted(p.stem for p in (ROOT / "build" / "variants").glob("*.so"))
+for B in [int(b) for b in os.environ.get('AB_SIZES', '125000').split(',')]:
+    for n in names:
+        env = dict(os.environ, AIRC_LIB=str(ROOT / "build" / "variants" / f"{n}.so"))
+        r = subprocess.run([sys.executable, "-c", CHILD, str(B)], env=env, capture_output=True, text=True)
+        print(f"{n:28s} B={B}: {r.stdout.strip() or r.stderr.strip()[-300:]}", flush=True)
