@@ -198,8 +198,15 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
   a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
   a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
   const int bs = 128;
+#ifdef AIRC_LIN_V1   // round-1 kernel: 16 lanes per node, everything recomputed per lane
   const long long threads = n * 16;
   linearize_kernel<<<(unsigned)((threads + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+#else
+  const long long threads = n * 8;
+  const unsigned grid = (unsigned)((threads + bs - 1) / bs);
+  if (layout == AIRC_LAYOUT_SOA) linearize_coop_kernel<8, true><<<grid, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  else linearize_coop_kernel<8, false><<<grid, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+#endif
   return check_launch();
 }
 

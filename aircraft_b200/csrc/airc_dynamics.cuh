@@ -169,11 +169,21 @@ AIRC_HD void surrogate(const FusedNet& net, float qbar, float alpha, float beta,
   }
 }
 
+// How the network is evaluated: by this thread alone (NetFull) or shared among the lanes that
+// cooperate on one node (NetCoop in airc_coop.cuh).
+struct NetFull {
+  const FusedNet* net;
+  template <bool WITH_JAC>
+  AIRC_HD void eval(float qbar, float alpha, float beta, const Ctl& c, float C[6], float J[6][5]) const {
+    surrogate<WITH_JAC>(*net, qbar, alpha, beta, c, C, J);
+  }
+};
+
 // f(x,u) without the trivial p_dot = v rows.  base.py:385-406.
-template <bool WITH_JAC>
-AIRC_HD void f_eval(const DevConst& P, const float v[3], const float q[4], const float w[3],
-                    const Ctl& c, float vdot[3], float qdot[4], float wdot[3], Stage& s,
-                    float J[6][5]) {
+template <bool WITH_JAC, class Net>
+AIRC_HD void f_eval_net(const DevConst& P, const Net& net, const float v[3], const float q[4],
+                        const float w[3], const Ctl& c, float vdot[3], float qdot[4], float wdot[3],
+                        Stage& s, float J[6][5]) {
   float n2;
   rot_matrix(q, s.M, n2);
   s.inv_n2 = rcp_nr(n2);
@@ -199,7 +209,7 @@ AIRC_HD void f_eval(const DevConst& P, const float v[3], const float q[4], const
     s.inv_cosb = fast_rsqrt(fmaf(-s.sb, s.sb, 1.0f));
   }
 
-  surrogate<WITH_JAC>(P.net, s.qbar, s.alpha, s.beta, c, s.C, J);
+  net.template eval<WITH_JAC>(s.qbar, s.alpha, s.beta, c, s.C, J);
   s.C[5] = fmaf(P.k_rudder, c.dr, s.C[5]);                  // coefficient_models.py:102-103
   s.sa = 1.0f;
   s.sbeta_s = 1.0f;
@@ -252,6 +262,13 @@ AIRC_HD void f_eval(const DevConst& P, const float v[3], const float q[4], const
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     wdot[i] = fmaf(P.Iinv[3 * i + 2], t[2], fmaf(P.Iinv[3 * i + 1], t[1], P.Iinv[3 * i] * t[0]));
+}
+
+template <bool WITH_JAC>
+AIRC_HD void f_eval(const DevConst& P, const float v[3], const float q[4], const float w[3],
+                    const Ctl& c, float vdot[3], float qdot[4], float wdot[3], Stage& s,
+                    float J[6][5]) {
+  f_eval_net<WITH_JAC>(P, NetFull{&P.net}, v, q, w, c, vdot, qdot, wdot, s, J);
 }
 
 // Directional derivative of f at the point described by (v,q,w,c,s,J) along

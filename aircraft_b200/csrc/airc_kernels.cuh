@@ -15,6 +15,7 @@
 #include <cuda_runtime.h>
 
 #include "airc_step.cuh"
+#include "airc_coop.cuh"
 
 namespace airc {
 
@@ -286,6 +287,94 @@ linearize_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
       for (int r = 0; r < 13; ++r)
 #pragma unroll
         for (int cc = 3; cc < 6; ++cc) o[(long long)(r * 7 + cc) * a.B_se] = 0.0f;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ K2 (cooperative)
+// L = 8 lanes per node, 4 nodes per warp.  Column slots 2*lane, 2*lane+1 (one packed tangent):
+//   slots 0..9   d/d(v, q, omega)      = A columns 3..12            (lanes 0..4)
+//   slots 10..13 d/d(aileron, elevator, rudder, flaps) = B columns 0,1,2,6   (lanes 5, 6)
+//   lane 7 carries no tangent work of its own: it writes x+ and the constant columns
+//   dPhi/dp = [I;0] and dPhi/d(thrust) = 0 (f does not read p; thrust is inert, aircraft.py:320).
+// The surrogate and its 6x5 Jacobian are shared: two hidden-unit pairs per lane, all-reduced by
+// shuffles (NetCoop).  The network lives in shared memory because each lane reads different pairs.
+#ifndef AIRC_LIN_MINBLOCKS
+#define AIRC_LIN_MINBLOCKS 2
+#endif
+// SOA is a template parameter so that the 26 column stores per lane use compile-time (AoS) or
+// single-stride (SoA: element stride n) addressing instead of generic 64-bit stride arithmetic.
+template <int L, bool SOA>
+__global__ void __launch_bounds__(128, AIRC_LIN_MINBLOCKS)
+linearize_coop_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
+  __shared__ FusedNet snet;
+  {
+    const float* src = reinterpret_cast<const float*>(&P.net);
+    float* dst = reinterpret_cast<float*>(&snet);
+    for (int i = threadIdx.x; i < (int)(sizeof(FusedNet) / sizeof(float)); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long node_raw = gt / L;
+  const int lane = (int)(gt % L);
+  const bool live = node_raw < a.n;
+  const long long node = live ? node_raw : a.n - 1;   // keep whole warps alive for the shuffles
+  State s;
+  load_state(a.x, node, s);
+  const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
+  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
+
+  const int s0 = 2 * lane, s1 = 2 * lane + 1;
+  TangentT<F2> D;
+  auto seed = [&](int slot) { return F2{s0 == slot ? 1.0f : 0.0f, s1 == slot ? 1.0f : 0.0f}; };
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { D.p[i] = F2{0.0f, 0.0f}; D.v[i] = seed(i); D.w[i] = seed(7 + i); }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) D.q[i] = seed(3 + i);
+  D.dc.da = seed(10); D.dc.de = seed(11); D.dc.dr = seed(12); D.dc.df = seed(13);
+
+  const NetCoop<L> net{&snet, lane};
+  state_update_lin<F2>(P, net, s, c, dt, a.substeps, a.normalise != 0, D);
+  if (!live) return;
+
+  F2 col[13];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { col[i] = D.p[i]; col[3 + i] = D.v[i]; col[10 + i] = D.w[i]; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) col[6 + i] = D.q[i];
+
+  // element (node, e) of A / Bm: SoA base[e*n + node], AoS base[node*E + e]
+  const long long es = SOA ? a.n : 1;                       // element stride
+  float* const Ab = a.A ? a.A + (SOA ? node : node * 169) : nullptr;
+  float* const Bb = a.Bm ? a.Bm + (SOA ? node : node * 91) : nullptr;
+  if (lane < 5) {
+    if (Ab) {
+      float* o = Ab + (3 + s0) * es;
+#pragma unroll
+      for (int r = 0; r < 13; ++r, o += 13 * es) { o[0] = col[r].lo; o[es] = col[r].hi; }
+    }
+  } else if (lane < 7) {
+    if (Bb) {
+      const int c0 = (lane == 5) ? 0 : 2, c1 = (lane == 5) ? 1 : 6;
+      float* o = Bb;
+#pragma unroll
+      for (int r = 0; r < 13; ++r, o += 7 * es) { o[c0 * es] = col[r].lo; o[c1 * es] = col[r].hi; }
+    }
+  } else {
+    if (a.xn.base) store_state(a.xn, node, s);
+    if (Ab) {
+      float* o = Ab;
+#pragma unroll
+      for (int r = 0; r < 13; ++r, o += 13 * es)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) o[cc * es] = (r == cc) ? 1.0f : 0.0f;
+    }
+    if (Bb) {
+      float* o = Bb + 3 * es;
+#pragma unroll
+      for (int r = 0; r < 13; ++r, o += 7 * es)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) o[cc * es] = 0.0f;
     }
   }
 }

@@ -118,6 +118,28 @@ AIRC_HD F2 mul2(const F2& a, const F2& b) {
 }
 AIRC_HD F2 bc2(float a) { return F2{a, a}; }
 
+// ---- one vocabulary for scalar (float) and packed (F2 = two tangent columns) arithmetic, so that the
+// forward-mode tangent code is written once.  Primal quantities stay scalar and enter packed
+// instructions as broadcast operands (free in SASS: "R.F32" operand form of FFMA2).
+AIRC_HD float tfma(float a, float b, float c) { return fmaf(a, b, c); }
+AIRC_HD F2 tfma(float a, const F2& b, const F2& c) { return fma2(bc2(a), b, c); }
+AIRC_HD F2 tfma(const F2& a, float b, const F2& c) { return fma2(a, bc2(b), c); }
+AIRC_HD F2 tfma(const F2& a, const F2& b, const F2& c) { return fma2(a, b, c); }
+AIRC_HD float tmul(float a, float b) { return a * b; }
+AIRC_HD F2 tmul(float a, const F2& b) { return mul2(bc2(a), b); }
+AIRC_HD F2 tmul(const F2& a, float b) { return mul2(a, bc2(b)); }
+AIRC_HD F2 tmul(const F2& a, const F2& b) { return mul2(a, b); }
+AIRC_HD float tadd(float a, float b) { return a + b; }
+AIRC_HD F2 tadd(const F2& a, const F2& b) { return add2(a, b); }
+AIRC_HD float tsub(float a, float b) { return a - b; }
+AIRC_HD F2 tsub(const F2& a, const F2& b) { return fma2(bc2(-1.0f), b, a); }
+template <class T> AIRC_HD T tzero();
+template <> AIRC_HD float tzero<float>() { return 0.0f; }
+template <> AIRC_HD F2 tzero<F2>() { return F2{0.0f, 0.0f}; }
+// a*b - c*d and a*b + c*d with scalar (primal) a, c
+template <class T> AIRC_HD T tdiff(float a, const T& b, float c, const T& d) { return tfma(a, b, tmul(-c, d)); }
+template <class T> AIRC_HD T tsum(float a, const T& b, float c, const T& d) { return tfma(a, b, tmul(c, d)); }
+
 // ---------------------------------------------------------------- logistic in base 2
 // The surrogate's tanh is evaluated as tanh(a) = 1 - 2 r, r = 1/(1 + 2^h), h = 2*log2(e)*a.
 // The factor 2*log2(e) is folded into the first-layer weights and the affine map t -> r into

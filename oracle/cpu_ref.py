@@ -98,6 +98,18 @@ class HostEmul:
         self.lib.emul_linearize.argtypes = [_PP, _NP, _f32, _f32, C.c_float, C.c_int64, C.c_int,
                                             C.c_uint32, _f32, _f32, _f32]
 
+        self.lib.emul_linearize_packed.argtypes = self.lib.emul_linearize.argtypes
+
+    def linearize_packed(self, x, u, dt, substeps=1, normalise=False):
+        """The cooperative kernel's arithmetic (packed two-column tangents), one lane per node."""
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        n = x.shape[0]
+        xn = np.empty((n, 13), np.float32)
+        A, Bm = np.zeros((n, 13, 13), np.float32), np.zeros((n, 13, 7), np.float32)
+        self.lib.emul_linearize_packed(C.byref(self.params), C.byref(self.blob), x, u, float(dt), n,
+                                       substeps, 1 if normalise else 0, xn, A, Bm)
+        return xn, A, Bm
+
     def surrogate(self, inp):
         inp = np.ascontiguousarray(inp, np.float32)
         out = np.empty((inp.shape[0], 6), np.float32)

@@ -9,6 +9,7 @@
 
 #include "../aircraft_b200/csrc/airc_fuse.hpp"
 #include "../aircraft_b200/csrc/airc_step.cuh"
+#include "../aircraft_b200/csrc/airc_coop.cuh"
 
 using namespace airc;
 
@@ -92,6 +93,46 @@ void emul_linearize(const AircParams* p, const AircNNBlob* nn, const float* x, c
         if (col < 13) A[(i * 13 + r) * 13 + col] = tp[r];
         else Bm[(i * 13 + r) * 7 + (col - 13)] = tp[r];
       }
+    }
+  }
+}
+
+// The K2 arithmetic: packed (two-column) tangents through rk4_step_lin with the cooperative network
+// policy degenerated to one lane (L = 1, no shuffles).  A[n][13][13], B[n][13][7].
+void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                           float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                           float* Bm) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  const NetCoop<1> net{&P.net, 0};
+  for (int64_t i = 0; i < n; ++i) {
+    for (int pair = 0; pair < 7; ++pair) {          // slots (0,1) .. (12,13) as in the kernel
+      State s; Ctl c;
+      load(x + 13 * i, u + 7 * i, s, c);
+      const int s0 = 2 * pair, s1 = 2 * pair + 1;
+      auto seed = [&](int slot) { return F2{s0 == slot ? 1.0f : 0.0f, s1 == slot ? 1.0f : 0.0f}; };
+      TangentT<F2> D;
+      for (int k = 0; k < 3; ++k) { D.p[k] = F2{0.f, 0.f}; D.v[k] = seed(k); D.w[k] = seed(7 + k); }
+      for (int k = 0; k < 4; ++k) D.q[k] = seed(3 + k);
+      D.dc.da = seed(10); D.dc.de = seed(11); D.dc.dr = seed(12); D.dc.df = seed(13);
+      state_update_lin<F2>(P, net, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, D);
+      if (pair == 0) store(s, xn + 13 * i);
+      F2 col[13];
+      for (int k = 0; k < 3; ++k) { col[k] = D.p[k]; col[3 + k] = D.v[k]; col[10 + k] = D.w[k]; }
+      for (int k = 0; k < 4; ++k) col[6 + k] = D.q[k];
+      static const int bcol[4] = {0, 1, 2, 6};
+      for (int r = 0; r < 13; ++r) {
+        const float vals[2] = {col[r].lo, col[r].hi};
+        for (int hlf = 0; hlf < 2; ++hlf) {
+          const int slot = 2 * pair + hlf;
+          if (slot < 10) A[(i * 13 + r) * 13 + 3 + slot] = vals[hlf];
+          else Bm[(i * 13 + r) * 7 + bcol[slot - 10]] = vals[hlf];
+        }
+      }
+    }
+    for (int r = 0; r < 13; ++r) {
+      for (int cc = 0; cc < 3; ++cc) A[(i * 13 + r) * 13 + cc] = (r == cc) ? 1.0f : 0.0f;
+      for (int cc = 3; cc < 6; ++cc) Bm[(i * 13 + r) * 7 + cc] = 0.0f;
     }
   }
 }

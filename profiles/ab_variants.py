@@ -21,6 +21,17 @@ x0 = torch.tensor(make_states(1, seed=4, level=True).T, dtype=torch.float32, dev
 U = device_control_sequences(torch, B, 200, seed=100, device=dev)
 ms = time_launches(torch, lambda: ac.rollout(x0, U, 0.01, layout="soa", return_final=False, cost=True), 10, 3)
 r = ac.rollout(x0, U, 0.01, layout="soa", return_final=False, cost=True)
+if len(sys.argv) > 2 and sys.argv[2] == "lin":
+    from aircraft_b200.workloads import make_controls
+    n = B
+    x = torch.tensor(make_states(n, seed=300, perturb_norm=1e-3).T, dtype=torch.float32, device=dev).contiguous()
+    u = torch.tensor(make_controls(n, seed=300).T, dtype=torch.float32, device=dev).contiguous()
+    ms = time_launches(torch, lambda: ac.linearize(x, u, 0.01, layout="soa"), 10, 3)
+    xa, ua = x.T.contiguous(), u.T.contiguous()
+    ms2 = time_launches(torch, lambda: ac.linearize(xa, ua, 0.01), 10, 3)
+    xn, A, Bm = ac.linearize(x, u, 0.01, layout="soa")
+    print("lin soa %%.4f ms %%.3e evals/s %%.0f GB/s | aos %%.4f ms %%.3e evals/s | checksum %%.6e" %% (ms, n/ms*1e3, n*1172/ms*1e3/1e9, ms2, n/ms2*1e3, float(A.double().abs().sum())))
+    sys.exit(0)
 print("%%.4f ms  %%.3e steps/s  %%.2f TFLOP/s  checksum %%.6e" %% (ms, B*200/ms*1e3, B*200*3953/ms*1e3/1e12, float(r.cost.nan_to_num(0).double().sum())))
 ''' % str(ROOT)
 
@@ -28,5 +39,5 @@ names = sys.argv[1:] or sorted(p.stem for p in (ROOT / "build" / "variants").glo
 for B in [int(b) for b in os.environ.get('AB_SIZES', '125000').split(',')]:
     for n in names:
         env = dict(os.environ, AIRC_LIB=str(ROOT / "build" / "variants" / f"{n}.so"))
-        r = subprocess.run([sys.executable, "-c", CHILD, str(B)], env=env, capture_output=True, text=True)
+        r = subprocess.run([sys.executable, "-c", CHILD, str(B)] + ([os.environ["AB_MODE"]] if os.environ.get("AB_MODE") else []), env=env, capture_output=True, text=True)
         print(f"{n:28s} B={B}: {r.stdout.strip() or r.stderr.strip()[-300:]}", flush=True)

@@ -126,8 +126,8 @@ def test_rollout_free_running_near_trim(ac, orc):
     X = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True).trajectory.double().cpu().numpy()
     Xo = orc.rollout(t64(x0), t64(U), 0.01, normalise=True).numpy()
     # trimmed states: omega and the lateral components start at ~0, so the column floor is a
-    # physical scale (0.1 m, m/s, rad/s; 0.1 on q), not the 1e-3 used for generic states
-    errs = [col_err(X[:, k], Xo[:, k], atol=0.1) for k in (1, 10, 50, 100)]
+    # physical scale (1 m, 1 m/s, 1 rad/s, 1 on q): absolute SI error, not the 1e-3 floor used for generic states
+    errs = [col_err(X[:, k], Xo[:, k], atol=1.0) for k in (1, 10, 50, 100)]
     print("free-running error growth (steps 1,10,50,100):", ["%.1e" % e for e in errs])
     assert errs[0] < PARITY_TOL and errs[-1] < 5e-3
 

@@ -50,3 +50,27 @@ def test_linearize(pair, substeps, normalise):
     # Jacobian entries: per-entry scale over the batch, floor 1e-3 of the matrix scale
     assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
     assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+
+
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (2, True)])
+def test_linearize_packed_tangents(pair, substeps, normalise):
+    """The cooperative K2 arithmetic: two Jacobian columns per packed tangent (f_tangent_t<F2>,
+    rk4_step_lin) with the network policy NetCoop<1>."""
+    emu, orc = pair
+    x, u = make_states(512, seed=24, perturb_norm=1e-3), make_controls(512, seed=24)
+    xn, A, B = emu.linearize_packed(x, u, 0.01, substeps, normalise)
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01, substeps, normalise)
+    assert col_err(xn, xo.numpy()) < PARITY_TOL
+    assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+
+
+def test_linearize_packed_with_stall_scaling(built):
+    p, blob = params_for(stall_scaling=True)
+    emu, orc = HostEmul(p, blob), oracle_for(stall_scaling=True)
+    x, u = make_states(256, seed=25), make_controls(256, seed=25)
+    x[:128, 3:6] *= np.array([0.6, 1.0, 2.0])
+    xn, A, B = emu.linearize_packed(x, u, 0.01)
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01)
+    assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
