@@ -11,7 +11,7 @@ def __getattr__(name):  # lazy: the CUDA library is loaded on first use of the c
     if name in ("Aircraft", "COEFF_MODEL_REGISTRY", "NeuralModel", "CoefficientModel"):
         from . import aircraft as _a
         return getattr(_a, name)
-    if name in ("ShardedRollout", "shard_range"):
+    if name in ("ShardedRollout", "shard_range", "sweep_sampled"):
         from . import sharding as _s
         return getattr(_s, name)
     raise AttributeError(name)

@@ -44,12 +44,25 @@ class AircCostParams(C.Structure):
     ]
 
 
+class AircSweepParams(C.Structure):
+    _fields_ = [
+        ("seed", C.c_uint64), ("index_offset", C.c_uint64),
+        ("sigma0", C.c_float * 4), ("sigma", C.c_float * 4),
+        ("lo", C.c_float * 4), ("hi", C.c_float * 4),
+        ("ckpt_interval", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+SWEEP_RECORD_HEADER = 4
+
 assert C.sizeof(AircNNBlob) == 860 * 4
+assert C.sizeof(AircSweepParams) == 88
 
 _vp, _i64, _i32, _u32, _f = C.c_void_p, C.c_int64, C.c_int, C.c_uint32, C.c_float
 _PP = C.POINTER(AircParams)
 _NP = C.POINTER(AircNNBlob)
 _CP = C.POINTER(AircCostParams)
+_SP = C.POINTER(AircSweepParams)
 
 # name -> (restype, argtypes); every symbol include/aircraft_b200.h declares
 PROTOTYPES = {
@@ -65,6 +78,13 @@ PROTOTYPES = {
     "airc_linearize": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                  _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
+    "airc_sweep_record_floats": (C.c_int64, [_i32]),
+    "airc_sweep_workspace_bytes": (C.c_size_t, [_i64, _i32, _i32]),
+    "airc_sweep": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _SP, _CP, _vp, C.c_size_t,
+                             _vp, _vp, _vp]),
+    "airc_select_record": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp]),
+    "airc_sweep_controls": (C.c_int, [_vp, _vp, _i32, _SP, _i64, _i64, _i32, _vp, _vp]),
+    "airc_sweep_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _SP, _CP, _vp, _vp]),
     "airc_measure_fp32_peak": (C.c_int, [_vp, _i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "airc_state_derivative_host": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
     "airc_state_update_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp]),

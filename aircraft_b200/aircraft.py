@@ -29,7 +29,7 @@ from . import _cabi
 from ._cabi import (FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX)
 from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH)
-from .params import load_nn_blob, make_cost_params, make_params
+from .params import load_nn_blob, make_cost_params, make_params, make_sweep_params
 
 try:  # torch is plumbing (device memory, streams); the numpy/host path does not need it
     import torch
@@ -79,6 +79,33 @@ class RolloutResult:
     final: Any = None          # [B,13] (aos) or [13,B] (soa)
     trajectory: Any = None     # [B,H+1,13] (aos) or [H+1,13,B] (soa)
     cost: Any = None           # [B]
+
+
+@dataclass
+class SweepRecord:
+    """The winner of a sampling sweep, decoded from the library's FP32 record."""
+    min_cost: Any = None         # 0-dim tensor / float
+    argmin: Any = None           # global trajectory index (0-dim int64 tensor / int)
+    trajectory: Any = None       # [H+1,13]
+    controls: Any = None         # [H,7]
+    cost: Any = None             # [B] when requested
+    raw: Any = None              # the undecoded record (what travels through the all-gather)
+    workspace: Any = None        # device scratch, reusable by the next sweep of the same size
+
+
+def decode_record(raw, H: int, cost=None) -> SweepRecord:
+    """Views into a record [4 + 13(H+1) + 7H] (torch tensor on any device, or numpy)."""
+    hdr = _cabi.SWEEP_RECORD_HEADER
+    nt = 13 * (H + 1)
+    if _is_torch(raw):
+        idx = raw[2:4].view(torch.int32).to(torch.int64)
+        gidx = (idx[0] & 0xFFFFFFFF) | (idx[1] << 32)
+        return SweepRecord(raw[0], gidx, raw[hdr:hdr + nt].view(H + 1, 13),
+                           raw[hdr + nt:hdr + nt + 7 * H].view(H, 7), cost, raw)
+    idx = raw[2:4].view(np.uint32)
+    gidx = int(idx[0]) | (int(idx[1]) << 32)
+    return SweepRecord(float(raw[0]), gidx, raw[hdr:hdr + nt].reshape(H + 1, 13),
+                       raw[hdr + nt:hdr + nt + 7 * H].reshape(H, 7), cost, raw)
 
 
 def _check(rc: int, lib, what: str):
@@ -453,6 +480,78 @@ class Aircraft:
                    lib, "airc_linearize_host")
             xn, A, Bm = (None if a is None else self._like(a, x) for a in (xn, A, Bm))
         return xn, A, Bm
+
+    # ------------------------------------------------------------------ sampling-MPC sweep
+    def sweep(self, x0, U_nom, dt: float, B: int, *, sampler=None, cost=True,
+              substeps: Optional[int] = None, normalise: Optional[bool] = None,
+              return_costs: bool = False, workspace=None) -> SweepRecord:
+        """B control sequences sampled IN THE KERNEL around ``U_nom[H,7]`` (counter-based
+        generator, see include/aircraft_b200.h), rolled out from the shared state ``x0[13]`` with
+        the fused primary MPC loss (main/control/control.py:35-93 for many candidates at once),
+        reduced to (min, arg-min) on the device; the winner's trajectory and controls come back
+        in one record.  Nothing is synchronised with the host on the device path.
+
+        sampler: None, a dict of make_sweep_params kwargs, or an AircSweepParams.
+        Host (numpy) inputs go through airc_sweep_host and return numpy results."""
+        sp = sampler if isinstance(sampler, _cabi.AircSweepParams) else make_sweep_params(**(sampler or {}))
+        cp = cost if isinstance(cost, _cabi.AircCostParams) else \
+            make_cost_params(**(cost if isinstance(cost, dict) else {}))
+        lib, h = self._lib, self.handle
+        ns, fl = self._substeps(substeps), self._flags(normalise)
+        B = int(B)
+        if B < 0:
+            raise RuntimeError("B must be >= 0")
+        on_dev = self._on_device(x0, U_nom)
+        if on_dev:
+            xd = self._dev32(x0 if _is_torch(x0) else torch.as_tensor(np.asarray(x0)).cuda(self._device), "x0").reshape(-1)
+            Ud = self._dev32(U_nom if _is_torch(U_nom) else torch.as_tensor(np.asarray(U_nom)).cuda(self._device), "U_nom")
+        else:
+            xd, Ud = self._host32(x0, "x0").reshape(-1), self._host32(U_nom, "U_nom")
+        if xd.shape[0] != NX:
+            raise RuntimeError(f"x0 must be one state [13], got {tuple(xd.shape)}")
+        if Ud.ndim != 2 or Ud.shape[1] != NU:
+            raise RuntimeError(f"U_nom must be [H,7], got {tuple(Ud.shape)}")
+        H = int(Ud.shape[0])
+        R = int(lib.airc_sweep_record_floats(H))
+        if on_dev:
+            dev = xd.device
+            need = int(lib.airc_sweep_workspace_bytes(B, H, sp.ckpt_interval))
+            if workspace is None or workspace.numel() < need:
+                workspace = torch.empty(need, dtype=torch.uint8, device=dev)
+            rec = torch.empty(R, dtype=torch.float32, device=dev)
+            cst = torch.empty(B, dtype=torch.float32, device=dev) if return_costs else None
+            _check(lib.airc_sweep(h, xd.data_ptr(), Ud.data_ptr(), float(dt), B, H, ns, fl, C.byref(sp),
+                                  C.byref(cp), workspace.data_ptr(), workspace.numel(), self._ptr(cst),
+                                  rec.data_ptr(), self._stream()), lib, "airc_sweep")
+            out = decode_record(rec, H, cst)
+            out.workspace = workspace
+            return out
+        rec = np.empty(R, np.float32)
+        cst = np.empty(B, np.float32) if return_costs else None
+        _check(lib.airc_sweep_host(h, xd.ctypes.data, Ud.ctypes.data, float(dt), B, H, ns, fl, C.byref(sp),
+                                   C.byref(cp), self._ptr(cst), rec.ctypes.data), lib, "airc_sweep_host")
+        return decode_record(rec, H, cst)
+
+    def sweep_controls(self, U_nom, sampler, first: int, count: int, layout: str = "aos"):
+        """The control sequences the sweep samples for trajectories [first, first+count):
+        [count,H,7] ('aos') or [H,7,count] ('soa'), on the device."""
+        sp = sampler if isinstance(sampler, _cabi.AircSweepParams) else make_sweep_params(**(sampler or {}))
+        Ud = self._dev32(U_nom if _is_torch(U_nom) else torch.as_tensor(np.asarray(U_nom)).cuda(self._device), "U_nom")
+        H = int(Ud.shape[0])
+        soa = layout == "soa"
+        U = torch.empty((H, 7, count) if soa else (count, H, 7), dtype=torch.float32, device=Ud.device)
+        _check(self._lib.airc_sweep_controls(self.handle, Ud.data_ptr(), H, C.byref(sp), int(first), int(count),
+                                             LAYOUT_SOA if soa else LAYOUT_AOS, U.data_ptr(), self._stream()),
+               self._lib, "airc_sweep_controls")
+        return U
+
+    def select_record(self, records):
+        """Best of n stacked records [n,R] (after an all-gather across ranks)."""
+        r = self._dev32(records, "records")
+        out = torch.empty(r.shape[1], dtype=torch.float32, device=r.device)
+        _check(self._lib.airc_select_record(self.handle, r.data_ptr(), r.shape[0], r.shape[1], out.data_ptr(),
+                                            self._stream()), self._lib, "airc_select_record")
+        return out
 
     def argmin(self, cost):
         """(min, argmin) of a device cost vector; ties resolve to the lower index, NaNs sort last."""

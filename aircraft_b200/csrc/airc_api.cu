@@ -10,6 +10,7 @@
 #include "airc_fuse.hpp"
 #include "airc_kernels.cuh"
 #include "airc_peak.cuh"
+#include "airc_sweep.cuh"
 
 using namespace airc;
 
@@ -69,7 +70,7 @@ int airc_version(void) { return 100; }
 
 const char* airc_build_info(void) {
   return "aircraft_b200 0.1.0 sm_100a (" __DATE__ " " __TIME__ ") kernels: state_derivative,"
-         " state_update, rollout, linearize, argmin";
+         " state_update, rollout, sweep, linearize, argmin";
 }
 
 const char* airc_last_error(const AircHandle*) { return g_err; }
@@ -226,6 +227,118 @@ int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_mi
   return check_launch();
 }
 
+// ------------------------------------------------------------------ sampling-MPC sweep
+static const double kSamplerStd = 147.80053;   // sqrt(4*(256^2-1)/12): std of a sum of four bytes
+
+static int ckpt_interval_of(int H, int requested) {
+  int C = requested > 0 ? requested : 8;
+  if (C > H) C = H > 0 ? H : 1;
+  while ((H + C - 1) / C > 1024) ++C;      // one winner thread per segment, one block
+  return C;
+}
+
+static CostConst make_cost_const(const AircCostParams* cp, int H) {
+  return CostConst{cp->goal[0], cp->goal[1], cp->vel_param, cp->w_goal, cp->w_du,
+                   (float)(-1.4426950408889634 / (double)cp->du_eps), cp->w_height,
+                   H > 0 ? cp->w_speed / (float)H : 0.f, cp->w_vx, cp->w_vyz};
+}
+
+static Sampler make_sampler(const AircSweepParams* sp) {
+  Sampler s;
+  for (int c = 0; c < 4; ++c) {
+    s.s0[c] = (float)((double)sp->sigma0[c] / kSamplerStd);
+    s.s[c] = (float)((double)sp->sigma[c] / kSamplerStd);
+    s.lo[c] = sp->lo[c];
+    s.hi[c] = sp->hi[c];
+  }
+  s.seed_lo_mixed = mix32((unsigned int)(sp->seed & 0xFFFFFFFFull));
+  s.seed_hi = (unsigned int)(sp->seed >> 32);
+  s.index_offset = sp->index_offset;
+  return s;
+}
+
+static size_t al256(size_t b) { return (b + 255) / 256 * 256; }
+
+int64_t airc_sweep_record_floats(int H) {
+  return H < 0 ? 0 : (int64_t)AIRC_SWEEP_RECORD_HEADER + 13LL * (H + 1) + 7LL * H;
+}
+
+size_t airc_sweep_workspace_bytes(int64_t B, int H, int ckpt_interval) {
+  if (B < 0 || H < 0) return 0;
+  const int C = ckpt_interval_of(H, ckpt_interval);
+  const int S = H > 0 ? (H + C - 1) / C : 1;
+  return 256 + al256((size_t)B * sizeof(float)) + al256((size_t)(S - 1) * 17 * (size_t)B * sizeof(float));
+}
+
+int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+               int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+               void* workspace, size_t workspace_bytes, float* cost, float* record, void* stream) {
+  if (!h || !x0 || (!U_nom && H > 0) || !sp || !cp || !record || B < 0 || B > 0xFFFFFFFFLL || H < 0 ||
+      substeps < 1 || (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
+    return fail(AIRC_EINVAL, "airc_sweep: bad argument%s", "");
+  const int C = ckpt_interval_of(H, sp->ckpt_interval);
+  const int S = H > 0 ? (H + C - 1) / C : 1;
+  const size_t need_min = 256;
+  if (!workspace || workspace_bytes < need_min)
+    return fail(AIRC_EINVAL, "airc_sweep: workspace too small (see airc_sweep_workspace_bytes)%s", "");
+  // checkpoints are used when the workspace has room for them; otherwise the winner is re-rolled
+  // sequentially (same result, H steps of latency instead of C)
+  const bool use_ckpt = S > 1 && workspace_bytes >= airc_sweep_workspace_bytes(B, H, C);
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = (char*)workspace;
+  unsigned long long* key = (unsigned long long*)ws;
+  float* thrust_du = (float*)(ws + 8);
+  float* ckpt = use_ckpt ? (float*)(ws + 256 + al256((size_t)B * sizeof(float))) : nullptr;
+  const CostConst cc = make_cost_const(cp, H);
+  const Sampler smp = make_sampler(sp);
+  sweep_prep_kernel<<<1, 32, 0, st>>>(U_nom, H, cc.neg_log2e_over_eps, key, thrust_du);
+  if (B > 0) {
+    SweepArgs a;
+    memset(&a, 0, sizeof(a));
+    a.x0 = x0; a.Unom = U_nom; a.cost = cost; a.ckpt = ckpt; a.key = key; a.thrust_du = thrust_du;
+    a.cc = cc; a.smp = smp; a.dt = dt; a.B = B; a.H = H; a.C = C; a.substeps = substeps;
+    a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+    const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : AIRC_ROLLOUT_BS);
+    const unsigned grid = (unsigned)((B + bs - 1) / bs);
+    if (use_ckpt) sweep_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
+    else sweep_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+  }
+  WinnerArgs w;
+  memset(&w, 0, sizeof(w));
+  w.x0 = x0; w.Unom = U_nom; w.ckpt = ckpt; w.key = key; w.smp = smp; w.record = record; w.dt = dt;
+  w.B = B; w.H = H; w.C = use_ckpt ? C : (H > 0 ? H : 1); w.substeps = substeps;
+  w.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+  const int wthreads = use_ckpt ? S : 1;
+  sweep_winner_kernel<<<(wthreads + 31) / 32, 32, 0, st>>>(h->dc, w);
+  return check_launch();
+}
+
+int airc_select_record(const AircHandle* h, const float* records, int n, int64_t record_floats,
+                       float* out_record, void* stream) {
+  if (!h || !records || !out_record || n < 1 || record_floats < AIRC_SWEEP_RECORD_HEADER)
+    return fail(AIRC_EINVAL, "airc_select_record: bad argument%s", "");
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  long long blocks = (record_floats + 255) / 256;
+  if (blocks > 64) blocks = 64;
+  select_record_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(records, n, record_floats, out_record);
+  return check_launch();
+}
+
+int airc_sweep_controls(const AircHandle* h, const float* U_nom, int H, const AircSweepParams* sp,
+                        int64_t first, int64_t count, int layout, float* U, void* stream) {
+  if (!h || (!U_nom && H > 0) || !sp || H < 0 || first < 0 || count < 0 || (layout != 0 && layout != 1) || (!U && count > 0 && H > 0))
+    return fail(AIRC_EINVAL, "airc_sweep_controls: bad argument%s", "");
+  if (count == 0 || H == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  sweep_controls_kernel<<<(unsigned)((count + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+      U_nom, H, make_sampler(sp), first, count, layout == AIRC_LAYOUT_SOA ? 1 : 0, U);
+  return check_launch();
+}
+
 int airc_measure_fp32_peak(const AircHandle* h, int repeats, double* tflops, double* ms) {
   if (!h || !tflops || repeats < 1) return fail(AIRC_EINVAL, "airc_measure_fp32_peak: bad argument%s", "");
   DeviceGuard g(h->device);
@@ -369,6 +482,34 @@ int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
   if (x_next) CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   if (A) CUDA_TRY(cudaMemcpyAsync(A, dA, 169 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   if (Bm) CUDA_TRY(cudaMemcpyAsync(Bm, dB, 91 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
+int airc_sweep_host(AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+                    int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+                    float* cost, float* record) {
+  if (!h || !x0 || (!U_nom && H > 0) || !sp || !cp || !record || B < 0 || H < 0)
+    return fail(AIRC_EINVAL, "airc_sweep_host: bad argument%s", "");
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t wsb = airc_sweep_workspace_bytes(B, H, sp->ckpt_interval);
+  const size_t R = (size_t)airc_sweep_record_floats(H);
+  const size_t bx = al(13), bU = al((size_t)7 * H), bR = al(R), bc = cost ? al((size_t)B) : 0;
+  int rc = ensure_scratch(h, bx + bU + bR + bc + wsb);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float* dx0 = (float*)base;
+  float* dU = (float*)(base + bx);
+  float* dR = (float*)(base + bx + bU);
+  float* dc = cost ? (float*)(base + bx + bU + bR) : nullptr;
+  void* ws = base + bx + bU + bR + bc;
+  CUDA_TRY(cudaMemcpyAsync(dx0, x0, 13 * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  if (H > 0) CUDA_TRY(cudaMemcpyAsync(dU, U_nom, (size_t)7 * H * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_sweep(h, dx0, dU, dt, B, H, substeps, flags, sp, cp, ws, wsb, dc, dR, h->hstream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(record, dR, R * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (cost && B > 0) CUDA_TRY(cudaMemcpyAsync(cost, dc, (size_t)B * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   CUDA_TRY(cudaStreamSynchronize(h->hstream));
   return AIRC_OK;
 }

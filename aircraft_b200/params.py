@@ -14,7 +14,7 @@ from typing import Sequence
 import numpy as np
 import torch
 
-from ._cabi import AircNNBlob, AircParams, AircCostParams
+from ._cabi import AircNNBlob, AircParams, AircCostParams, AircSweepParams
 from .config import AircraftConfiguration, DEFAULT_MODEL_PATH, inertia_about_com
 
 _BLOB_FIELDS = [
@@ -81,3 +81,20 @@ def make_cost_params(goal=(150.0, 0.0), vel_param=1.0, w_goal=1000.0, w_du=100.0
     c.vel_param, c.w_goal, c.w_du, c.du_eps = float(vel_param), float(w_goal), float(w_du), float(du_eps)
     c.w_height, c.w_speed, c.w_vx, c.w_vyz = float(w_height), float(w_speed), float(w_vx), float(w_vyz)
     return c
+
+
+def make_sweep_params(seed: int = 0, index_offset: int = 0, sigma0=(1.0, 1.0, 1.0, 0.1),
+                      sigma=(0.25, 0.25, 0.25, 0.025), lo=(-5.0, -5.0, -5.0, 0.0),
+                      hi=(5.0, 5.0, 5.0, 1.0), ckpt_interval: int = 0) -> AircSweepParams:
+    """Sampler of the sampling-MPC sweep (include/aircraft_b200.h, AircSweepParams): per live
+    control (aileron, elevator, rudder, flaps) the std of the initial offset and of the random-walk
+    increment, and the actuator limits (/root/reference/src/aircraft/control/aircraft.py:24,29-41:
+    +-5 deg, flaps in [0,1])."""
+    s = AircSweepParams()
+    s.seed, s.index_offset = int(seed) & 0xFFFFFFFFFFFFFFFF, int(index_offset)
+    s.sigma0[:] = [float(v) for v in sigma0]
+    s.sigma[:] = [float(v) for v in sigma]
+    s.lo[:] = [float(v) for v in lo]
+    s.hi[:] = [float(v) for v in hi]
+    s.ckpt_interval = int(ckpt_interval)
+    return s

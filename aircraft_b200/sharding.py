@@ -124,6 +124,49 @@ class ShardedRollout:
         return SweepResult(gmin, gidx, owner, traj, ctrl, cost_local, all_cost)
 
 
+def select_record_torch(records: torch.Tensor) -> torch.Tensor:
+    """Best of n stacked sweep records [n,R]: lowest orderable cost (word 1), ties to the lower
+    global index (words 2-3), NaN last -- the rule of select_record_kernel, in torch ops, for
+    records that live on the host (gloo tests, host-side callers)."""
+    r = records.contiguous()
+    words = r[:, 1:4].contiguous().view(torch.int32).to(torch.int64) & 0xFFFFFFFF
+    keys = [(int(w[0]), int(w[1]) | (int(w[2]) << 32)) for w in words.tolist()]
+    best = min(range(len(keys)), key=lambda i: keys[i])
+    return r[best]
+
+
+def sweep_sampled(aircraft, x0, U_nom, dt: float, total: int, *, sampler=None, cost=True,
+                  substeps: Optional[int] = None, normalise: Optional[bool] = None, group=None,
+                  workspace=None, return_costs: bool = False):
+    """BASELINE config 4 over the ranks of `group`: `total` control sequences sampled in the
+    kernel, contiguous index ranges per rank (the sampler is keyed on the GLOBAL trajectory
+    index, so the candidate set does not depend on the sharding), one all-gather of the per-rank
+    winner records (16 kB each) and a device-side selection.  No host synchronisation."""
+    from .aircraft import decode_record
+    from .params import make_sweep_params
+    from . import _cabi
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    start, stop = shard_range(total, rank, world)
+    if isinstance(sampler, _cabi.AircSweepParams):
+        sp = _cabi.AircSweepParams.from_buffer_copy(sampler)
+    else:
+        sp = make_sweep_params(**(sampler or {}))
+    base = int(sp.index_offset)
+    sp.index_offset = base + start
+    local = aircraft.sweep(x0, U_nom, dt, stop - start, sampler=sp, cost=cost, substeps=substeps,
+                           normalise=normalise, workspace=workspace, return_costs=return_costs)
+    if world == 1:
+        return local
+    H = local.controls.shape[0]
+    allrec = torch.empty((world, local.raw.numel()), dtype=torch.float32, device=local.raw.device)
+    dist.all_gather_into_tensor(allrec, local.raw.reshape(1, -1), group=group)
+    best = aircraft.select_record(allrec) if allrec.is_cuda else select_record_torch(allrec)
+    out = decode_record(best, H, local.cost)
+    out.workspace = local.workspace
+    return out
+
+
 def gather_varlen(local: torch.Tensor, total: int, rank: int, world: int, group=None) -> torch.Tensor:
     """all_gather of contiguous shards whose lengths follow shard_range (differ by at most one)."""
     if world == 1:

@@ -150,6 +150,58 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
 int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
                 int64_t* out_idx, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Sampling-MPC sweep (BASELINE config 4): B control sequences are SAMPLED IN THE KERNEL around one
+ * nominal sequence, rolled out from one shared initial state with the fused cost, reduced to
+ * (min, arg-min) by warp shuffles + one 64-bit atomicMin per warp, and the winner's trajectory
+ * and controls are reproduced from sparse state checkpoints -- no control tensor ever exists in
+ * memory and nothing is synchronised with the host.  It replaces, for many candidate sequences
+ * at once, the reference's rollout loop + loss of main/control/control.py:35-93.
+ *
+ * Sampler (counter-based, a pure function of (seed, global trajectory index g, step k, slot c);
+ * slots c = 0..3 are the four controls the NN path reads: aileron, elevator, rudder, flaps;
+ * thrust rows are inert in the dynamics (aircraft.py:320) and stay at their nominal values):
+ *   mix32(x): x ^= x>>16; x *= 0x7feb352d; x ^= x>>15; x *= 0x846ca68b; x ^= x>>16   (uint32)
+ *   tkey   = mix32((uint32)g + mix32((uint32)seed)) ^ (uint32)(seed>>32)
+ *   w(k,c) = mix32(tkey + k*0x9E3779B9 + c*0x7F4A7C15)
+ *   n(k,c) = byte0(w)+byte1(w)+byte2(w)+byte3(w) - 510          (integer in [-510,510], ~N(0,147.8^2))
+ *   d_0    = s0_c*n(0,c);  d_k = fmaf(s_c, n(k,c), d_{k-1})     (FP32; s = (float)(sigma/147.80053))
+ *   u_k[c] = min(max(U_nom[k][c] + d_k, lo_c), hi_c)
+ * oracle/cpu_ref.cpp restates the same generator, so every sampled sequence can be regenerated
+ * bit-identically on the host. */
+typedef struct AircSweepParams {
+  uint64_t seed;
+  uint64_t index_offset;  /* global index of this shard's trajectory 0 (sampler and arg-min use it) */
+  float sigma0[4];        /* std of the initial offset d_0: aileron, elevator, rudder, flaps */
+  float sigma[4];         /* std of the random-walk increment per step */
+  float lo[4];
+  float hi[4];
+  int32_t ckpt_interval;  /* state checkpoint every this many steps; 0 = default (8) */
+  int32_t reserved;
+} AircSweepParams;
+
+/* The winner's record, FP32 words: [0] min cost, [1] its orderable bit pattern (uint32),
+ * [2..3] global arg-min (int64), then trajectory [H+1][13], then controls [H][7]. */
+#define AIRC_SWEEP_RECORD_HEADER 4
+int64_t airc_sweep_record_floats(int H);
+/* bytes of device workspace airc_sweep needs (checkpoints dominate: 17 floats x B per checkpoint) */
+size_t airc_sweep_workspace_bytes(int64_t B, int H, int ckpt_interval);
+
+/* x0 [13], U_nom [H][7], workspace, cost (optional, [B]) and record are DEVICE pointers. */
+int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+               int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+               void* workspace, size_t workspace_bytes, float* cost, float* record, void* stream);
+
+/* Picks the best of n records (lowest cost, ties to the lower global index, NaN last) laid out
+ * with a stride of record_floats -- the step after an all-gather of per-rank records. */
+int airc_select_record(const AircHandle* h, const float* records, int n, int64_t record_floats,
+                       float* out_record, void* stream);
+
+/* The controls the sweep samples for trajectories [first, first+count): U [count][H][7] (AoS) or
+ * [H][7][count] (SoA), device memory -- for inspection and for the parity tests. */
+int airc_sweep_controls(const AircHandle* h, const float* U_nom, int H, const AircSweepParams* sp,
+                        int64_t first, int64_t count, int layout, float* U, void* stream);
+
 /* Measures the device's FP32 FFMA throughput (independent fused multiply-adds, all SMs, best of
  * `repeats` launches, CUDA events): the roofline denominator of the rollout kernel, which no
  * vendor library reports.  Synchronises.  ms (optional) receives the best launch time. */
@@ -169,6 +221,10 @@ int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, 
 int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
                         const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                         int layout, float* x_next, float* A, float* Bm);
+
+int airc_sweep_host(AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+                    int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+                    float* cost, float* record);
 
 #ifdef __cplusplus
 }

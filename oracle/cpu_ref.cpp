@@ -189,6 +189,72 @@ template <class T> void phi(const Model& m, T x[13], const T u[7], const T& dt, 
   if (normalise) normalise_q(x);
 }
 
+// ---------------------------------------------------------------- primary MPC loss
+// main/control/control.py:35-70 restated for one trajectory X[H+1][13], U[H][7]:
+//   1000|p_N[:2]-goal|^2 + 100 sum_{k,i}(1-exp(-du^2/1e-2)) + (z_N-z_0)^2
+//   - sum_{k<N} |v_b(x_k)|^2/(100 N) + vel_param*1000*vx_N + 1000(vy_N^2+vz_N^2)
+double body_speed2(const Model& m, const double x[13]) {
+  const double* v = x + 3; const double* q = x + 6;
+  double qi[4], vq[4] = {v[0], v[1], v[2], 0.0}, t1[4], t2[4];
+  qinv(q, qi); qmul(qi, vq, t1); qmul(t1, q, t2);          // base.py:156-159
+  double acc = 0.0;
+  for (int i = 0; i < 3; ++i) { const double c = t2[i] + m.p.epsilon; acc += c * c; }
+  return acc;
+}
+
+struct CostAcc {
+  double sum_du = 0.0, sum_v2 = 0.0, z0 = 0.0;
+  double uprev[7];
+  void node(const Model& m, const AircCostParams& cp, const double x[13], const double u[7], int k) {
+    if (k == 0) z0 = x[2];
+    else for (int i = 0; i < 7; ++i) { const double d = u[i] - uprev[i]; sum_du += 1.0 - exp(-d * d / (double)cp.du_eps); }
+    for (int i = 0; i < 7; ++i) uprev[i] = u[i];
+    sum_v2 += body_speed2(m, x);
+  }
+  double finish(const AircCostParams& cp, const double xN[13], int H) const {
+    const double ex = xN[0] - cp.goal[0], ey = xN[1] - cp.goal[1], ez = xN[2] - z0;
+    return cp.w_goal * (ex * ex + ey * ey) + cp.w_du * sum_du + cp.w_height * ez * ez -
+           (H > 0 ? cp.w_speed / H : 0.0) * sum_v2 + cp.vel_param * cp.w_vx * xN[3] +
+           cp.w_vyz * (xN[4] * xN[4] + xN[5] * xN[5]);
+  }
+};
+
+// ---------------------------------------------------------------- sweep sampler
+// The counter-based generator specified in include/aircraft_b200.h (AircSweepParams), restated.
+// Control values are FP32 by specification (the product generates them in FP32 registers).
+inline uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16;
+  return x;
+}
+struct SweepGen {
+  float s0[4], s[4], lo[4], hi[4];
+  uint32_t seed_lo_mixed, seed_hi;
+  explicit SweepGen(const AircSweepParams& sp) {
+    for (int c = 0; c < 4; ++c) {
+      s0[c] = (float)((double)sp.sigma0[c] / 147.80053);
+      s[c] = (float)((double)sp.sigma[c] / 147.80053);
+      lo[c] = sp.lo[c]; hi[c] = sp.hi[c];
+    }
+    seed_lo_mixed = mix32((uint32_t)(sp.seed & 0xFFFFFFFFull));
+    seed_hi = (uint32_t)(sp.seed >> 32);
+  }
+  uint32_t tkey(uint64_t g) const { return mix32((uint32_t)g + seed_lo_mixed) ^ seed_hi; }
+  // advances the walk offsets d to step k, writes the 7 controls of that step
+  __attribute__((optimize("fp-contract=off")))
+  void step(uint32_t tk, int k, const float* unom_k, float d[4], float u[7]) const {
+    static const int chan[4] = {0, 1, 2, 6};
+    for (int c = 0; c < 7; ++c) u[c] = unom_k[c];
+    const uint32_t cnt = tk + (uint32_t)k * 0x9E3779B9U;
+    for (int c = 0; c < 4; ++c) {
+      const uint32_t w = mix32(cnt + (uint32_t)c * 0x7F4A7C15U);
+      const float n = (float)((int)((w & 255U) + ((w >> 8) & 255U) + ((w >> 16) & 255U) + (w >> 24)) - 510);
+      d[c] = (k == 0) ? s0[c] * n : fmaf(s[c], n, d[c]);
+      const float t = unom_k[chan[c]] + d[c];
+      u[chan[c]] = fminf(fmaxf(t, lo[c]), hi[c]);
+    }
+  }
+};
+
 int set_threads(int threads) {
 #ifdef _OPENMP
   if (threads > 0) omp_set_num_threads(threads);
@@ -264,6 +330,75 @@ void cpuref_linearize(const AircParams* p, const AircNNBlob* nn, const double* x
       if (Bm) for (int k = 0; k < 7; ++k) Bm[(i * 13 + r) * 7 + k] = s[r].d[13 + k];
     }
   }
+}
+
+// costs of explicit control sequences: x0[B][13], U[B][H][7] (or shared [H][7]) -> cost[B]
+void cpuref_rollout_cost(const AircParams* p, const AircNNBlob* nn, const double* x0, const double* U,
+                         double dt, int64_t B, int H, int substeps, uint32_t flags,
+                         const AircCostParams* cp, double* cost, int threads) {
+  Model m; make_model(p, nn, m); set_threads(threads);
+#pragma omp parallel for schedule(static)
+  for (int64_t b = 0; b < B; ++b) {
+    double s[13]; memcpy(s, x0 + 13 * b, sizeof(s));
+    const double* Ub = (flags & AIRC_FLAG_SHARED_U) ? U : U + (int64_t)7 * H * b;
+    CostAcc acc;
+    for (int k = 0; k < H; ++k) {
+      acc.node(m, *cp, s, Ub + 7 * k, k);
+      phi<double>(m, s, Ub + 7 * k, dt, substeps, flags & AIRC_FLAG_NORMALISE);
+    }
+    if (H == 0) acc.z0 = s[2];
+    cost[b] = acc.finish(*cp, s, H);
+  }
+}
+
+// the sampled control sequences of trajectories [first, first+count): U[count][H][7] FP32
+void cpuref_sweep_controls(const AircSweepParams* sp, const float* Unom, int H, int64_t first,
+                           int64_t count, float* U, int threads) {
+  const SweepGen gen(*sp); set_threads(threads);
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < count; ++i) {
+    const uint32_t tk = gen.tkey(sp->index_offset + (uint64_t)(first + i));
+    float d[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < H; ++k) gen.step(tk, k, Unom + 7 * k, d, U + ((int64_t)i * H + k) * 7);
+  }
+}
+
+// The whole sampling-MPC sweep on the CPU: sample, roll out (float64), cost, (min, arg-min).
+// x0[13], Unom[H][7] (FP32, as the product receives it); cost[B] optional.  Returns the arg-min
+// (local index) through best_idx and the minimum through best_cost.
+void cpuref_sweep(const AircParams* p, const AircNNBlob* nn, const double* x0, const float* Unom,
+                  double dt, int64_t B, int H, int substeps, uint32_t flags, const AircSweepParams* sp,
+                  const AircCostParams* cp, double* cost, double* best_cost, int64_t* best_idx,
+                  int threads) {
+  Model m; make_model(p, nn, m); set_threads(threads);
+  const SweepGen gen(*sp);
+  double gbest = INFINITY; int64_t gidx = -1;
+#pragma omp parallel
+  {
+    double lbest = INFINITY; int64_t lidx = -1;
+#pragma omp for schedule(static) nowait
+    for (int64_t b = 0; b < B; ++b) {
+      double s[13]; memcpy(s, x0, sizeof(s));
+      const uint32_t tk = gen.tkey(sp->index_offset + (uint64_t)b);
+      float d[4] = {0.f, 0.f, 0.f, 0.f}, uf[7];
+      double u[7];
+      CostAcc acc;
+      for (int k = 0; k < H; ++k) {
+        gen.step(tk, k, Unom + 7 * k, d, uf);
+        for (int c = 0; c < 7; ++c) u[c] = uf[c];
+        acc.node(m, *cp, s, u, k);
+        phi<double>(m, s, u, dt, substeps, flags & AIRC_FLAG_NORMALISE);
+      }
+      if (H == 0) acc.z0 = s[2];
+      const double J = acc.finish(*cp, s, H);
+      if (cost) cost[b] = J;
+      if (J < lbest) { lbest = J; lidx = b; }
+    }
+#pragma omp critical
+    if (lidx >= 0 && (lbest < gbest || (lbest == gbest && lidx < gidx))) { gbest = lbest; gidx = lidx; }
+  }
+  if (best_cost) *best_cost = gbest;
+  if (best_idx) *best_idx = gidx;
 }
 
 }  // extern "C"

@@ -14,7 +14,7 @@ from pathlib import Path
 
 import numpy as np
 
-from aircraft_b200._cabi import AircNNBlob, AircParams
+from aircraft_b200._cabi import AircCostParams, AircNNBlob, AircParams, AircSweepParams
 
 HERE = Path(__file__).resolve().parent
 _f64 = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
@@ -48,6 +48,47 @@ class CpuRef:
                                             C.c_int, C.c_uint32, vp, vp, C.c_int]
         self.lib.cpuref_linearize.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
                                               C.c_uint32, _f64, _f64, _f64, C.c_int]
+
+        _CPp, _SPp = C.POINTER(AircCostParams), C.POINTER(AircSweepParams)
+        self.lib.cpuref_rollout_cost.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
+                                                 C.c_int, C.c_uint32, _CPp, _f64, C.c_int]
+        self.lib.cpuref_sweep_controls.argtypes = [_SPp, _f32, C.c_int, C.c_int64, C.c_int64, _f32, C.c_int]
+        self.lib.cpuref_sweep.argtypes = [_PP, _NP, _f64, _f32, C.c_double, C.c_int64, C.c_int, C.c_int,
+                                          C.c_uint32, _SPp, _CPp, vp, C.POINTER(C.c_double),
+                                          C.POINTER(C.c_int64), C.c_int]
+
+    def rollout_cost(self, x0, U, dt, cost_params, substeps=1, normalise=False):
+        """Primary MPC loss (main/control/control.py:35-70) of explicit control sequences."""
+        x0, U = np.ascontiguousarray(x0, np.float64), np.ascontiguousarray(U, np.float64)
+        B = x0.shape[0]
+        flags = (1 if normalise else 0) | (2 if U.ndim == 2 else 0)
+        H = U.shape[0] if U.ndim == 2 else U.shape[1]
+        out = np.empty(B)
+        self.lib.cpuref_rollout_cost(*self._pb(), x0, U, float(dt), B, H, substeps, flags,
+                                     C.byref(cost_params), out, self.threads)
+        return out
+
+    def sweep_controls(self, sweep_params, U_nom, first, count):
+        """The sampled control sequences [count,H,7] (FP32) of trajectories [first, first+count)."""
+        U_nom = np.ascontiguousarray(U_nom, np.float32)
+        H = U_nom.shape[0]
+        U = np.empty((count, H, 7), np.float32)
+        self.lib.cpuref_sweep_controls(C.byref(sweep_params), U_nom, H, first, count, U, self.threads)
+        return U
+
+    def sweep(self, x0, U_nom, dt, B, sweep_params, cost_params, substeps=1, normalise=False,
+              return_costs=True):
+        """Whole sampling sweep on the CPU -> (min cost, arg-min (local index), cost[B] or None)."""
+        x0 = np.ascontiguousarray(x0, np.float64).reshape(13)
+        U_nom = np.ascontiguousarray(U_nom, np.float32)
+        H = U_nom.shape[0]
+        cost = np.empty(B) if return_costs else None
+        bc, bi = C.c_double(), C.c_int64()
+        self.lib.cpuref_sweep(*self._pb(), x0, U_nom, float(dt), B, H, substeps, 1 if normalise else 0,
+                              C.byref(sweep_params), C.byref(cost_params),
+                              cost.ctypes.data if return_costs else None, C.byref(bc), C.byref(bi),
+                              self.threads)
+        return bc.value, bi.value, cost
 
     def _pb(self):
         return C.byref(self.params), C.byref(self.blob)
@@ -99,6 +140,16 @@ class HostEmul:
                                             C.c_uint32, _f32, _f32, _f32]
 
         self.lib.emul_linearize_packed.argtypes = self.lib.emul_linearize.argtypes
+        self.lib.emul_sweep_controls.argtypes = [C.POINTER(AircSweepParams), _f32, C.c_int, C.c_int64,
+                                                 C.c_int64, _f32]
+
+    def sweep_controls(self, sweep_params, U_nom, first, count):
+        """The product's own sampler code (airc_sampler.cuh) compiled for the host."""
+        U_nom = np.ascontiguousarray(U_nom, np.float32)
+        H = U_nom.shape[0]
+        U = np.empty((count, H, 7), np.float32)
+        self.lib.emul_sweep_controls(C.byref(sweep_params), U_nom, H, first, count, U)
+        return U
 
     def linearize_packed(self, x, u, dt, substeps=1, normalise=False):
         """The cooperative kernel's arithmetic (packed two-column tangents), one lane per node."""

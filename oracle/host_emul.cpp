@@ -10,6 +10,7 @@
 #include "../aircraft_b200/csrc/airc_fuse.hpp"
 #include "../aircraft_b200/csrc/airc_step.cuh"
 #include "../aircraft_b200/csrc/airc_coop.cuh"
+#include "../aircraft_b200/csrc/airc_sampler.cuh"
 
 using namespace airc;
 
@@ -136,4 +137,29 @@ void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const floa
     }
   }
 }
+
+// the product's sampler (airc_sampler.cuh) on the host: U[count][H][7]
+void emul_sweep_controls(const AircSweepParams* sp, const float* Unom, int H, int64_t first,
+                         int64_t count, float* U) {
+  Sampler s;
+  for (int c = 0; c < 4; ++c) {
+    s.s0[c] = (float)((double)sp->sigma0[c] / 147.80053);
+    s.s[c] = (float)((double)sp->sigma[c] / 147.80053);
+    s.lo[c] = sp->lo[c]; s.hi[c] = sp->hi[c];
+  }
+  s.seed_lo_mixed = mix32((unsigned int)(sp->seed & 0xFFFFFFFFull));
+  s.seed_hi = (unsigned int)(sp->seed >> 32);
+  s.index_offset = sp->index_offset;
+  for (int64_t i = 0; i < count; ++i) {
+    const unsigned int tk = traj_key(s.seed_lo_mixed, s.seed_hi, s.index_offset + (unsigned long long)(first + i));
+    float d[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < H; ++k) {
+      float un[4];
+      sample_step(s, tk, k, Unom + 7 * k, d, un);
+      float* o = U + ((int64_t)i * H + k) * 7;
+      for (int c = 0; c < 7; ++c) o[c] = Unom[7 * k + c];
+      o[0] = un[0]; o[1] = un[1]; o[2] = un[2]; o[6] = un[3];
+    }
+  }
 }
+}  // extern "C"
