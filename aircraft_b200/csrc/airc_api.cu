@@ -9,13 +9,17 @@
 #include "../../include/aircraft_b200.h"
 #include "airc_fuse.hpp"
 #include "airc_kernels.cuh"
+#include "airc_kernels2.cuh"
 #include "airc_peak.cuh"
 #include "airc_sweep.cuh"
+#include "airc_sweep2.cuh"
 
 using namespace airc;
 
 struct AircHandle {
   DevConst dc;
+  UnitNet un;          // the surrogate in unit-major order for the packed (two-trajectory) kernels
+  int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0 / 2: force scalar / packed
   int device;
   int sm_count;
   // used only by the *_host entry points (those are not re-entrant per handle)
@@ -93,6 +97,8 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   AircHandle* h = new (std::nothrow) AircHandle;
   if (!h) return fail(AIRC_ENOMEM, "airc_create: out of host memory%s", "");
   build_devconst(*params, *nn, h->dc);
+  make_unit_net(h->dc.net, h->un);
+  if (const char* e = getenv("AIRC_ROLLOUT_IMPL")) h->packed = atoi(e) == 1 ? 0 : 2;   // 0 scalar only, 1 auto, 2 packed always
   h->device = device;
   h->sm_count = prop.multiProcessorCount;
   *out = h;
@@ -172,6 +178,19 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
   const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : AIRC_ROLLOUT_BS);
   const unsigned grid = (unsigned)((B + bs - 1) / bs);
   cudaStream_t st = (cudaStream_t)stream;
+  // Explicit-control rollouts: the packed kernel (two trajectories per thread, 12 warps/SM) wins once
+  // the batch fills at least two of its waves (2 x 113 664 on a B200); below that the one-trajectory
+  // kernel's finer wave granularity wins (profiles/r1_variants_packed.txt).  AIRC_ROLLOUT_IMPL=1|2
+  // forces one of them (A/B timing).
+  const long long wave2 = (long long)h->sm_count * 3 * AIRC_R2_BS * 2;
+  if (h->packed == 2 || (h->packed == 1 && B >= 2 * wave2)) {
+    const unsigned grid2 = (unsigned)((B + 2 * AIRC_R2_BS - 1) / (2 * AIRC_R2_BS));
+    if (cost && X) rollout2_kernel<true, true><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
+    else if (cost) rollout2_kernel<true, false><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
+    else if (X) rollout2_kernel<false, true><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
+    else rollout2_kernel<false, false><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
+    return check_launch();
+  }
   if (cost && X) rollout_kernel<true, true><<<grid, bs, 0, st>>>(h->dc, a);
   else if (cost) rollout_kernel<true, false><<<grid, bs, 0, st>>>(h->dc, a);
   else if (X) rollout_kernel<false, true><<<grid, bs, 0, st>>>(h->dc, a);
@@ -263,11 +282,39 @@ int64_t airc_sweep_record_floats(int H) {
   return H < 0 ? 0 : (int64_t)AIRC_SWEEP_RECORD_HEADER + 13LL * (H + 1) + 7LL * H;
 }
 
+struct SweepLayout {
+  size_t off_ckpt, off_slice, off_flag, total;
+  int C, NS;
+  long long G64;
+};
+// workspace: [0,256) key | thrust_du | task counter ; checkpoints ; slice records ; group flags
+static SweepLayout sweep_layout(int64_t B, int H, int ckpt_interval) {
+  SweepLayout L;
+  L.C = ckpt_interval_of(H, ckpt_interval);
+  L.NS = H > 0 ? (H + L.C - 1) / L.C : 1;
+  L.G64 = (B + 31) / 32;                     // flags are sized for the 32-trajectory grouping
+  L.off_ckpt = 256;
+  L.off_slice = L.off_ckpt + al256((size_t)(L.NS - 1) * 17 * (size_t)B * sizeof(float));
+  L.off_flag = L.off_slice + al256((size_t)23 * (size_t)B * sizeof(float));
+  L.total = L.off_flag + al256((size_t)L.G64 * sizeof(int));
+  return L;
+}
+
 size_t airc_sweep_workspace_bytes(int64_t B, int H, int ckpt_interval) {
   if (B < 0 || H < 0) return 0;
-  const int C = ckpt_interval_of(H, ckpt_interval);
-  const int S = H > 0 ? (H + C - 1) / C : 1;
-  return 256 + al256((size_t)B * sizeof(float)) + al256((size_t)(S - 1) * 17 * (size_t)B * sizeof(float));
+  return sweep_layout(B, H, ckpt_interval).total;
+}
+
+// segments that minimise ceil(G S / W)/S (+ a small per-segment hand-over cost)
+static int choose_segments(long long G, long long W, int H) {
+  if (G <= W || H < 2) return 1;
+  int best = 1;
+  double be = 1e30;
+  for (int S = 1; S <= 32 && S <= H; ++S) {
+    const double e = (double)((G * S + W - 1) / W) / S + 0.003 * S;
+    if (e < be - 1e-12) { be = e; best = S; }
+  }
+  return best;
 }
 
 int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
@@ -284,15 +331,59 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
   // checkpoints are used when the workspace has room for them; otherwise the winner is re-rolled
   // sequentially (same result, H steps of latency instead of C)
   const bool use_ckpt = S > 1 && workspace_bytes >= airc_sweep_workspace_bytes(B, H, C);
+  const size_t ckpt_off = sweep_layout(B, H, sp->ckpt_interval).off_ckpt;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   cudaStream_t st = (cudaStream_t)stream;
   char* ws = (char*)workspace;
   unsigned long long* key = (unsigned long long*)ws;
   float* thrust_du = (float*)(ws + 8);
-  float* ckpt = use_ckpt ? (float*)(ws + 256 + al256((size_t)B * sizeof(float))) : nullptr;
+  float* ckpt = use_ckpt ? (float*)(ws + ckpt_off) : nullptr;
   const CostConst cc = make_cost_const(cp, H);
   const Sampler smp = make_sampler(sp);
+  if (h->packed) {
+    const SweepLayout L = sweep_layout(B, H, sp->ckpt_interval);
+    const bool full = workspace_bytes >= L.total;
+    const bool ck = full && L.NS > 1;
+    int* flag = full ? (int*)(ws + L.off_flag) : nullptr;
+    int per_sm = 0;
+    if (ck) CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sweep2_kernel<true>, AIRC_S2_BS, 0));
+    else CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sweep2_kernel<false>, AIRC_S2_BS, 0));
+    const long long slots = (long long)h->sm_count * (per_sm > 0 ? per_sm : 1);    // resident blocks
+    const long long W = slots * (AIRC_S2_BS / 32);                                 // resident warps
+    Sweep2Args a;
+    memset(&a, 0, sizeof(a));
+    // small sweeps: 32 trajectories per warp (hi halves idle) so that twice as many warps share the
+    // work, and one warp per block so that it spreads over all SMs
+    a.gs = (B <= W * 32) ? 32 : 64;
+    a.G = (int)((B + a.gs - 1) / a.gs);
+    const int bs = (a.G <= slots) ? 32 : AIRC_S2_BS;
+    a.GB = (a.G + bs / 32 - 1) / (bs / 32);
+    a.S = full ? choose_segments(a.GB, bs == 32 ? slots * (AIRC_S2_BS / 32) : slots, H) : 1;
+    if (const char* e = getenv("AIRC_SWEEP_SEGMENTS")) { if (full && atoi(e) > 0) a.S = atoi(e); }   // timing experiments
+    a.L = a.S > 1 ? (H + a.S - 1) / a.S : (H > 0 ? H : 1);
+    a.S = H > 0 ? (H + a.L - 1) / a.L : 1;
+    a.x0 = x0; a.Unom = U_nom; a.cost = cost; a.key = key; a.thrust_du = thrust_du;
+    a.ckpt = ck ? (float*)(ws + L.off_ckpt) : nullptr;
+    a.slice = full ? (float*)(ws + L.off_slice) : nullptr;
+    a.flag = flag;
+    a.cc = cc; a.smp = smp; a.dt = dt; a.B = B; a.H = H; a.C = L.C; a.substeps = substeps;
+    a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+    sweep2_prep_kernel<<<1, 256, 0, st>>>(U_nom, H, cc.neg_log2e_over_eps, key, thrust_du, flag, full ? a.G : 0);
+    if (B > 0) {
+      const unsigned grid = (unsigned)((long long)a.GB * a.S);
+      if (ck) sweep2_kernel<true><<<grid, bs, 0, st>>>(h->dc, h->un, a);
+      else sweep2_kernel<false><<<grid, bs, 0, st>>>(h->dc, h->un, a);
+    }
+    WinnerArgs w;
+    memset(&w, 0, sizeof(w));
+    w.x0 = x0; w.Unom = U_nom; w.ckpt = a.ckpt; w.key = key; w.smp = smp; w.record = record; w.dt = dt;
+    w.B = B; w.H = H; w.C = ck ? L.C : (H > 0 ? H : 1); w.substeps = substeps;
+    w.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+    const int wthreads = ck ? L.NS : 1;
+    sweep_winner2_kernel<<<(wthreads + 31) / 32, 32, 0, st>>>(h->dc, h->un, w);
+    return check_launch();
+  }
   sweep_prep_kernel<<<1, 32, 0, st>>>(U_nom, H, cc.neg_log2e_over_eps, key, thrust_du);
   if (B > 0) {
     SweepArgs a;

@@ -68,11 +68,12 @@ def test_sweep_costs_match_explicit_kernel_and_cpu_reference(ac, ref, x0):
     sp, cp = make_sweep_params(seed=11), make_cost_params()
     r = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
     cost = r.cost.cpu().numpy().astype(np.float64)
-    # (1) the explicit-control kernel on the regenerated sequences: same arithmetic path
+    # (1) the explicit-control kernel on the regenerated sequences (one-trajectory-per-thread kernel
+    #     at this size: same mathematics, different rounding)
     U = ac.sweep_controls(f32(Un), sp, 0, B, layout="soa")
     xs = f32(np.repeat(x0[:, None], B, 1))
     e = ac.rollout(xs, U, DT, layout="soa", cost=cp, return_final=False).cost.cpu().numpy().astype(np.float64)
-    assert np.abs(cost - e).max() <= 2e-6 * np.abs(e).max()
+    assert np.abs(cost - e).max() <= 1e-5 * np.abs(e).max()
     # (2) float64 CPU reference of the whole sweep (its own sampler, its own loss)
     bc, bi, c64 = ref.sweep(x0, Un, DT, B, sp, cp, normalise=True)
     assert np.abs(cost - c64).max() <= 1e-5 * np.abs(c64).max()
@@ -88,7 +89,7 @@ def test_sweep_costs_match_explicit_kernel_and_cpu_reference(ac, ref, x0):
     Xw = ref.rollout(x0[None], Uw[None].astype(np.float64), DT, normalise=True)[0]
     assert col_err(r.trajectory.cpu().numpy(), Xw) < 5e-5      # 40 free-running FP32 steps
     one = ac.rollout(f32(x0[None]), f32(Uw[None]), DT, return_trajectory=True).trajectory[0]
-    assert col_err(r.trajectory.cpu().numpy(), one.cpu().numpy()) < 2e-6
+    assert col_err(r.trajectory.cpu().numpy(), one.cpu().numpy()) < 2e-5
 
 
 @pytest.mark.parametrize("ckpt", [1, 7, 8, 40, 1000])
@@ -180,8 +181,66 @@ def test_full_size_shard_properties(ac, x0):
     Uw = ac.sweep_controls(f32(Un), sp, am, 1)
     assert torch.equal(Uw[0], r.controls)
     one = ac.rollout(f32(x0[None]), Uw, DT, return_trajectory=True, cost=True)
-    assert col_err(r.trajectory.cpu().numpy(), one.trajectory[0].cpu().numpy()) < 5e-6
-    assert abs(one.cost.item() - r.min_cost.item()) <= 2e-6 * abs(r.min_cost.item())
+    assert col_err(r.trajectory.cpu().numpy(), one.trajectory[0].cpu().numpy()) < 1e-4      # 200 free FP32 steps, two kernels
+    assert abs(one.cost.item() - r.min_cost.item()) <= 1e-4 * abs(r.min_cost.item())
     # determinism
     r2 = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, return_costs=True)
     assert torch.equal(r2.raw, r.raw) and torch.equal(r2.cost, cost)
+
+
+# ---------------------------------------------------------------- packed (two-trajectory) rollout kernel
+@pytest.fixture(scope="module")
+def ac_packed(built):
+    """A handle whose explicit-control rollouts are forced onto the packed kernel (by default it is
+    chosen for batches of >= 2 waves only)."""
+    import os
+    from aircraft_b200 import Aircraft
+    os.environ["AIRC_ROLLOUT_IMPL"] = "2"
+    try:
+        a = Aircraft.from_problem(com=TRIM_COM, device=DEV, physical_integration_substeps=1, normalise=True)
+        a.handle          # airc_create reads the knob
+    finally:
+        del os.environ["AIRC_ROLLOUT_IMPL"]
+    return a
+
+
+def test_packed_rollout_parity_and_lane_independence(ac_packed, ac, ref):
+    n, H = 2049, 30       # odd batch: the last thread has a dead hi half
+    x0s = make_states(n, seed=77, perturb_norm=1e-3)
+    U = make_control_sequences(n, H, seed=77)
+    r = ac_packed.rollout(f32(x0s), f32(U), DT, return_trajectory=True, cost=True)
+    Xr = ref.rollout(x0s, U, DT, normalise=True)
+    got = r.trajectory.cpu().numpy()
+    assert col_err(got[:, 1], Xr[:, 1]) < 1e-5                      # one step: the 1e-5 bar
+    assert col_err(got, Xr, batch_axes=(0, 1)) < 5e-5               # 30 free-running FP32 steps
+    cr = ref.rollout_cost(x0s, U, DT, make_cost_params(), normalise=True)
+    assert np.abs(r.cost.cpu().numpy() - cr).max() <= 1e-5 * np.abs(cr).max()
+    # substeps and no normalisation
+    r4 = ac_packed.rollout(f32(x0s[:500]), f32(U[:500, :5]), 0.05, substeps=4, normalise=False, return_trajectory=True)
+    X4 = ref.rollout(x0s[:500], U[:500, :5], 0.05, substeps=4, normalise=False)
+    assert col_err(r4.trajectory.cpu().numpy(), X4, batch_axes=(0, 1)) < 2e-5
+    # a trajectory's bits do not depend on its lane partner or on the batch it is part of
+    for j in (0, 31, 32, 1000, n - 1):
+        one = ac_packed.rollout(f32(x0s[j:j + 1]), f32(U[j:j + 1]), DT, return_trajectory=True, cost=True)
+        assert torch.equal(one.trajectory[0], r.trajectory[j]) and torch.equal(one.cost[0], r.cost[j])
+    # SoA == AoS, final state == last trajectory row
+    rs = ac_packed.rollout(f32(x0s.T), f32(U.transpose(1, 2, 0)), DT, layout="soa", return_trajectory=True, cost=True)
+    assert torch.equal(rs.trajectory.permute(2, 0, 1), r.trajectory) and torch.equal(rs.cost, r.cost)
+    assert torch.equal(r.final, r.trajectory[:, -1])
+    # NaN stays in its own trajectory (lane partner 32 untouched)
+    xb = x0s.copy(); xb[0, 6:10] = np.nan
+    rb = ac_packed.rollout(f32(xb), f32(U), DT, cost=True)
+    assert torch.isnan(rb.cost[0]) and torch.equal(rb.cost[1:], r.cost[1:])
+
+
+def test_sweep_equals_packed_explicit_rollout(ac_packed, x0):
+    B, H = 4096 + 17, 40
+    Un = nominal(H)
+    sp, cp = make_sweep_params(seed=11), make_cost_params()
+    r = ac_packed.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
+    U = ac_packed.sweep_controls(f32(Un), sp, 0, B, layout="soa")
+    e = ac_packed.rollout(f32(np.repeat(x0[:, None], B, 1)), U, DT, layout="soa", cost=cp, return_trajectory=True)
+    # identical arithmetic except the summation order of the (shared) thrust-row penalty
+    assert (r.cost - e.cost).abs().max().item() <= 2e-6 * e.cost.abs().max().item()
+    am = int(r.argmin.item())
+    assert torch.equal(e.trajectory[:, :, am], r.trajectory)
