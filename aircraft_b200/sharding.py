@@ -137,7 +137,7 @@ def select_record_torch(records: torch.Tensor) -> torch.Tensor:
 
 def sweep_sampled(aircraft, x0, U_nom, dt: float, total: int, *, sampler=None, cost=True,
                   substeps: Optional[int] = None, normalise: Optional[bool] = None, group=None,
-                  workspace=None, return_costs: bool = False):
+                  workspace=None, return_costs: bool = False, on_local=None):
     """BASELINE config 4 over the ranks of `group`: `total` control sequences sampled in the
     kernel, contiguous index ranges per rank (the sampler is keyed on the GLOBAL trajectory
     index, so the candidate set does not depend on the sharding), one all-gather of the per-rank
@@ -156,6 +156,8 @@ def sweep_sampled(aircraft, x0, U_nom, dt: float, total: int, *, sampler=None, c
     sp.index_offset = base + start
     local = aircraft.sweep(x0, U_nom, dt, stop - start, sampler=sp, cost=cost, substeps=substeps,
                            normalise=normalise, workspace=workspace, return_costs=return_costs)
+    if on_local is not None:
+        on_local()          # e.g. a CUDA event that separates the local kernels from the exchange
     if world == 1:
         return local
     H = local.controls.shape[0]

@@ -9,10 +9,15 @@ the CPU path on the box's host cores.
 A "step" is one pass of the hot path over one batch of synthetic input:
   workload c4 (default, every N): the per-GPU shard of BASELINE config 4, the sampling-MPC sweep
       "1M control-sequence rollouts x horizon 200 sharded over 8 B200" = 125 000 rollouts x 200
-      RK4 steps per GPU from one shared initial state, fused rollout+cost kernel, device arg-min,
-      then (N>1) the NCCL exchange of (min, arg-min) and broadcast of the winner's trajectory.
-      Weak scaling: at N=8 the job is exactly config 4.  Inputs (700 MB of control sequences per
-      GPU) are larger than the 126 MB L2, so nothing is cached between timed iterations.
+      RK4 steps per GPU from one shared initial state.  The control sequences are SAMPLED IN THE
+      KERNEL around one nominal sequence (counter-based generator keyed on the global trajectory
+      index, include/aircraft_b200.h), rolled out with the fused loss, reduced to (min, arg-min) by
+      warp shuffles, and the winner's trajectory is reproduced from state checkpoints; for N>1
+      the per-rank winner records (16 kB) are all-gathered over NCCL and selected on the device.
+      Weak scaling: at N=8 the job is exactly config 4.  The kernel reads 5.7 kB per launch and
+      streams > 126 MB of checkpoints through L2, so nothing is cached between timed iterations.
+      The same shard with EXPLICIT control tensors (700 MB per GPU, PCIe-bound end to end) is
+      reported under "extra".c4_explicit.
   workload c2: BASELINE config 2, 4096 rollouts x 200 from trim states on each GPU (a latency
       case: 128 warps on 592 SM sub-partitions); always reported under "extra" at N=1.
   Jacobians: BASELINE config 3 (65 536 x 100 nodes) and config 5's per-GPU shard (51 200 nodes),
@@ -134,17 +139,36 @@ def _cpu_sample_inputs(n: int, horizon: int):
     return x0, U
 
 
+def sweep_inputs():
+    """The shared initial state and nominal control sequence of the sweep (host, float32/64)."""
+    from aircraft_b200.workloads import make_control_sequences, make_states
+    x0 = make_states(1, seed=4, level=True)[0]
+    Un = make_control_sequences(1, H_ROLL, seed=4, sigma=0.05)[0].astype(np.float32)
+    return x0, Un
+
+
+def sweep_sampler(seed: int = 2025, offset: int = 0):
+    from aircraft_b200.params import make_sweep_params
+    return make_sweep_params(seed=seed, index_offset=offset)
+
+
+def cpu_sweep_once(ref, n: int):
+    """One CPU pass of the same job: sample n control sequences with the same generator, roll them
+    out in float64, loss, (min, arg-min)."""
+    from aircraft_b200.params import make_cost_params
+    x0, Un = sweep_inputs()
+    t = time.perf_counter()
+    ref.sweep(x0, Un, DT, n, sweep_sampler(), make_cost_params(), normalise=True, return_costs=False)
+    return time.perf_counter() - t
+
+
 def cpu_rollout_rate(ref, seconds: float, horizon: int = H_ROLL):
-    """state-steps/s of the CPU restatement on a bounded sample of the c4/c2 workload: calibrate
-    on one trajectory per thread, then size the sample to ~`seconds` of work."""
+    """state-steps/s of the CPU restatement on a bounded sample of the c4 workload: calibrate on
+    one trajectory per thread, then size the sample to ~`seconds` of work."""
     n0 = max(ref.threads, 1)
-    x0, U = _cpu_sample_inputs(n0, horizon)
-    t = time.perf_counter(); ref.rollout(x0, U, DT, normalise=True, trajectory=False); t0 = time.perf_counter() - t
-    per_traj = max(t0, 1e-4)      # one trajectory per thread in parallel
-    reps = int(max(1, min(4096, seconds / per_traj)))
-    n = n0 * reps
-    x0, U = _cpu_sample_inputs(n, horizon)
-    t = time.perf_counter(); ref.rollout(x0, U, DT, normalise=True, trajectory=False); el = time.perf_counter() - t
+    per_traj = max(cpu_sweep_once(ref, n0), 1e-4)      # one trajectory per thread in parallel
+    n = n0 * int(max(1, min(4096, seconds / per_traj)))
+    el = cpu_sweep_once(ref, n)
     return n * horizon / el, n, el
 
 
@@ -170,13 +194,11 @@ def run_reference(args):
     # size one step to ~2 s so that K+W steps end within a few minutes
     rate, _, _ = cpu_rollout_rate(ref, 1.0)
     n = int(max(ref.threads, min(per_gpu, rate * 2.0 / H_ROLL)))
-    x0, U = _cpu_sample_inputs(n, H_ROLL)
     for _ in range(args.warmup):
-        ref.rollout(x0, U, DT, normalise=True, trajectory=False)
-    t = time.perf_counter()
+        cpu_sweep_once(ref, n)
+    el = 0.0
     for _ in range(args.steps):
-        ref.rollout(x0, U, DT, normalise=True, trajectory=False)
-    el = time.perf_counter() - t
+        el += cpu_sweep_once(ref, n)
     value = n * H_ROLL * args.steps / el
     jrate, jn, _ = cpu_jacobian_rate(ref, 3.0)
     line = {
@@ -186,8 +208,9 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args.workload, per_gpu, args.gpus),
         "cpu_baseline": {"value": value, "unit": "state-steps/s", "cores": ref.threads, "kind": "port",
-                         "sample": f"{n} rollouts x {H_ROLL} steps per step (of {per_gpu} per GPU), "
-                                   "oracle/cpu_ref.cpp float64 OpenMP; the reference's CasADi VM cannot run here"},
+                         "sample": f"{n} sampled rollouts x {H_ROLL} steps per step (of {per_gpu} per GPU), same "
+                                   "sampler + loss + arg-min, oracle/cpu_ref.cpp float64 OpenMP; the "
+                                   "reference's CasADi VM cannot run here"},
         "jacobian": {"value": jrate, "unit": "jacobian-evals/s", "sample": f"{jn} nodes, 20-direction forward mode"},
         "e2e": {"value": value, "unit": "state-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -199,12 +222,14 @@ def workload_config(workload: str, per_gpu: int, gpus: int):
     if workload == "c4":
         name = (f"BASELINE config 4 shard: sampling-MPC sweep, {per_gpu} control-sequence rollouts x "
                 f"horizon {H_ROLL} per GPU from one shared state ({per_gpu * gpus} total; "
-                f"1M total at 8 GPUs), fused cost + arg-min + best-trajectory exchange")
+                f"1M total at 8 GPUs), controls sampled in the kernel, fused cost + arg-min + "
+                f"best-trajectory record exchange")
     else:
         name = f"BASELINE config 2: {per_gpu} rollouts x horizon {H_ROLL} from trim states per GPU"
     return {"workload": name, "rollouts_per_gpu": per_gpu, "horizon": H_ROLL, "dt": DT,
             "substeps": 1, "normalise": True, "layout": "soa", "parallelism": f"dp{gpus}",
-            "l2_policy": "inputs larger than L2 (700 MB of control sequences per GPU per step)"
+            "l2_policy": "no reusable inputs: each launch reads 5.7 kB and streams > 126 MB of checkpoint/"
+                         "slice records through L2, which evicts everything between timed iterations"
             if workload == "c4" else "L2 flushed between timed iterations (256 MB write)"}
 
 
@@ -247,7 +272,6 @@ def run_native(args):
     import torch.distributed as dist
     from aircraft_b200 import Aircraft
     from aircraft_b200.config import TRIM_COM
-    from aircraft_b200.sharding import ShardedRollout
     from aircraft_b200.workloads import make_states, trim_states
 
     if not torch.cuda.is_available():
@@ -263,22 +287,9 @@ def run_native(args):
         print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
 
     ac = Aircraft.from_problem(com=TRIM_COM, device=local, physical_integration_substeps=1, normalise=True)
-    sr = ShardedRollout(ac)
     per_gpu = args.per_gpu or (C4_TOTAL // C4_GPUS if args.workload == "c4" else 4096)
     total = per_gpu * world
     H, K, W = H_ROLL, args.steps, max(args.warmup, 3)
-    launches = 0
-
-    # ---- inputs resident in HBM before the timed region
-    if args.workload == "c4":
-        x1 = make_states(1, seed=4, level=True)
-        x0 = torch.tensor(x1.T, dtype=torch.float32, device=dev).expand(13, per_gpu).contiguous()
-    else:
-        xs, _ = trim_states(ac, per_gpu, seed=rank)
-        x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
-    U = device_control_sequences(torch, per_gpu, H, seed=100 + rank, device=dev)
-    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev) if args.workload == "c2" else None
-    torch.cuda.synchronize()
 
     clocks = ClockSampler(local)
     if rank == 0:
@@ -290,19 +301,89 @@ def run_native(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- `value`: device-resident inputs, whole step = fused rollout+cost, arg-min, exchange
+    if args.workload == "c2":
+        line = run_c2(torch, dist, ac, dev, rank, world, per_gpu, K, W, clocks, windows, barrier)
+    else:
+        line = run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, windows, barrier)
+
+    # ---- side measurements on rank 0 / every rank (no collectives inside)
+    extra = {}
+    if not args.no_extras:
+        extra.update(side_measurements(torch, ac, dev, rank, args))
+        if "c3" in extra:
+            line["jacobian"] = extra.pop("c3")
+    if rank == 0 and world == 1:
+        ref = _cpu_ref()
+        rate, n, sec = cpu_rollout_rate(ref, args.cpu_seconds)
+        line["cpu_baseline"] = {"value": rate, "unit": "state-steps/s", "cores": ref.threads, "kind": "port",
+                                "sample": f"{n} sampled rollouts x {H} steps ({sec:.1f} s) of the same workload "
+                                          "(same sampler, loss and arg-min), oracle/cpu_ref.cpp float64 OpenMP "
+                                          "(CasADi cannot run on this box)"}
+        if "jacobian" in line:
+            jr, jn, js = cpu_jacobian_rate(ref, 4.0)
+            line["jacobian"]["cpu_baseline"] = {"value": jr, "unit": "jacobian-evals/s", "cores": ref.threads,
+                                                "kind": "port", "sample": f"{jn} nodes ({js:.1f} s)"}
+    if extra:
+        line["extra"] = extra
+    if rank == 0:
+        clocks.stop()
+        line["clocks"] = clocks.summary(windows)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def fp32_peak(ac):
+    """FP32 FFMA peak of this device, measured now (MEASURED_PEAKS.json has no CUDA-core entry)."""
+    import ctypes as C
+    tf, ms = C.c_double(), C.c_double()
+    ac._lib.airc_measure_fp32_peak(ac.handle, 5, C.byref(tf), C.byref(ms))
+    return float(tf.value)
+
+
+def rollout_roofline(kernel, tflops, peak, steps_per_launch, ms_kernel, ms_step, note=""):
+    return {"kernel": kernel, "bound": "fp32", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+            "frac": tflops / peak,
+            "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); "
+                           "MEASURED_PEAKS.json has no FP32 CUDA-core entry",
+            "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": tflops / FP32_NOMINAL_TFLOPS,
+            "flops_per_state_step": F_STEP, "state_steps_per_launch": steps_per_launch,
+            "kernel_ms": ms_kernel, "kernel_share_of_step": ms_kernel / ms_step, "traffic": None,
+            "note": note}
+
+
+def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, windows, barrier):
+    """BASELINE config 4 (shard): sampling sweep with in-kernel control sampling."""
+    from aircraft_b200.params import make_cost_params
+    from aircraft_b200.sharding import sweep_sampled
+    H = H_ROLL
+    x0_np, Un_np = sweep_inputs()
+    x0_h = torch.tensor(x0_np, dtype=torch.float32).pin_memory()
+    Un_h = torch.tensor(Un_np, dtype=torch.float32).pin_memory()
+    x0_d, Un_d = x0_h.to(dev), Un_h.to(dev)
+    sp, cp = sweep_sampler(), make_cost_params()
+    ws = None
+    torch.cuda.synchronize()
+
+    # ---- `value`: inputs resident in HBM; whole step = sweep (prep + time-sliced rollout/cost/arg-min
+    #      kernel + winner re-roll) and, for N>1, the all-gather of records + device-side selection
     roll_events = []
 
     def step(record: bool):
-        if flush is not None:
-            flush.add_(1.0)
+        nonlocal ws
         if record:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        res = ac.rollout(x0, U, DT, layout="soa", return_final=False, cost=True)
-        if record:
-            e1.record(); roll_events.append((e0, e1))
-        return sr.finish_sweep(res.cost, x0, U, DT, total, layout="soa")
+        if world > 1:
+            out = sweep_sampled(ac, x0_d, Un_d, DT, total, sampler=sp, cost=cp, workspace=ws, on_local=(
+                (lambda: (e1.record(), roll_events.append((e0, e1)))) if record else None))
+        else:
+            out = ac.sweep(x0_d, Un_d, DT, per_gpu, sampler=sp, cost=cp, workspace=ws)
+            if record:
+                e1.record(); roll_events.append((e0, e1))
+        ws = out.workspace
+        return out
 
     for _ in range(W):
         out = step(False)
@@ -322,29 +403,25 @@ def run_native(args):
         ms_total = float(t.item())
     ms_step = ms_total / K
     value = total * H / (ms_step * 1e-3)
-    launches += K * (1 + 2 + 1)      # rollout, argmin (+finish), winner re-roll
+    launches = K * (3 + (1 if world > 1 else 0))      # prep, sweep2, winner2 (+ select_record)
     ms_roll = sum(a.elapsed_time(b) for a, b in roll_events) / K
     roll_tflops = per_gpu * H * F_STEP / (ms_roll * 1e-3) / 1e12
+    peak = fp32_peak(ac)
 
-    # ---- FP32 FMA peak of this device, measured now (no vendor number in MEASURED_PEAKS.json)
-    import ctypes as C
-    tf, ms = C.c_double(), C.c_double()
-    ac._lib.airc_measure_fp32_peak(ac.handle, 5, C.byref(tf), C.byref(ms))
-    fp32_peak = float(tf.value)
-
-    # ---- `e2e`: the same step through the host-buffer C ABI (airc_rollout_host): pinned host
-    #      inputs copied H2D, kernel, per-trajectory costs copied D2H, arg-min on the host
-    x0_h = torch.empty((13, per_gpu), dtype=torch.float32).pin_memory()
-    U_h = torch.empty((H, 7, per_gpu), dtype=torch.float32).pin_memory()
-    x0_h.copy_(x0); U_h.copy_(U)
-    x0_np, U_np = x0_h.numpy(), U_h.numpy()
-    h2d = x0_np.nbytes + U_np.nbytes
-    d2h = 4 * per_gpu
-    Ke = max(3, min(K, 10))
+    # ---- `e2e`: host buffers in, host record out, every step.  N=1: the C-ABI host entry point
+    #      (airc_sweep_host); N>1: pinned host -> device copies, sweep, exchange, record -> host.
+    h2d = x0_h.numel() * 4 + Un_h.numel() * 4
+    d2h = int(out.raw.numel()) * 4
+    Ke = max(3, min(K, 20))
+    x0_pin, Un_pin = x0_h.numpy(), Un_h.numpy()
 
     def e2e_step():
-        r = ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
-        return int(np.nanargmin(r.cost))
+        if world == 1:
+            r = ac.sweep(x0_pin, Un_pin, DT, per_gpu, sampler=sp, cost=cp)
+            return r.min_cost
+        xd, ud = x0_h.to(dev, non_blocking=True), Un_h.to(dev, non_blocking=True)
+        r = sweep_sampled(ac, xd, ud, DT, total, sampler=sp, cost=cp, workspace=ws)
+        return float(r.raw.cpu()[0])
 
     for _ in range(2):
         e2e_step()
@@ -361,52 +438,60 @@ def run_native(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         el = float(t.item())
     e2e_value = total * H * Ke / el
-    del x0_h, U_h
 
-    line = {
+    return {
         "metric": "surrogate RK4 state-steps/s", "value": value, "unit": "state-steps/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.workload, per_gpu, world),
+        "config": workload_config("c4", per_gpu, world),
         "e2e": {"value": e2e_value, "unit": "state-steps/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": Ke,
-                "path": "airc_rollout_host (C ABI, pinned host buffers) + host arg-min"},
+                "path": "airc_sweep_host (C ABI, host buffers in, winner record out)" if world == 1 else
+                        "pinned host -> device, airc_sweep, NCCL all-gather of records, airc_select_record, record -> host"},
         "gpu_launches": launches,
-        "roofline": {"kernel": "rollout_kernel<cost>", "bound": "fp32", "achieved": roll_tflops,
-                     "peak": fp32_peak, "unit": "TFLOP/s", "frac": roll_tflops / fp32_peak,
-                     "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); "
-                                    "MEASURED_PEAKS.json has no FP32 CUDA-core entry",
-                     "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": roll_tflops / FP32_NOMINAL_TFLOPS,
-                     "flops_per_state_step": F_STEP, "state_steps_per_launch": per_gpu * H,
-                     "kernel_ms": ms_roll, "kernel_share_of_step": ms_roll / ms_step,
-                     "traffic": None},
+        "best": {"min_cost": float(out.min_cost), "argmin": int(out.argmin)},
+        "roofline": rollout_roofline("sweep2_kernel<ckpt> (+ sweep2_prep, sweep_winner2: < 2 % of the call)",
+                                     roll_tflops, peak, per_gpu * H, ms_roll, ms_step,
+                                     "kernel_ms = CUDA events around the airc_sweep call (three launches)"),
     }
 
-    # ---- side measurements on rank 0 / every rank (no collectives inside)
-    extra = {}
-    if not args.no_extras:
-        extra.update(side_measurements(torch, ac, dev, rank, args))
-        if "c3" in extra:
-            line["jacobian"] = extra.pop("c3")
-    if rank == 0 and world == 1:
-        ref = _cpu_ref()
-        rate, n, sec = cpu_rollout_rate(ref, args.cpu_seconds)
-        line["cpu_baseline"] = {"value": rate, "unit": "state-steps/s", "cores": ref.threads, "kind": "port",
-                                "sample": f"{n} rollouts x {H} steps ({sec:.1f} s) of the same workload, "
-                                          "oracle/cpu_ref.cpp float64 OpenMP (CasADi cannot run on this box)"}
-        if "jacobian" in line:
-            jr, jn, js = cpu_jacobian_rate(ref, 4.0)
-            line["jacobian"]["cpu_baseline"] = {"value": jr, "unit": "jacobian-evals/s", "cores": ref.threads,
-                                                "kind": "port", "sample": f"{jn} nodes ({js:.1f} s)"}
-    if extra:
-        line["extra"] = extra
-    if rank == 0:
-        clocks.stop()
-        line["clocks"] = clocks.summary(windows)
-        print(json.dumps(line), flush=True)
+
+def run_c2(torch, dist, ac, dev, rank, world, per_gpu, K, W, clocks, windows, barrier):
+    """BASELINE config 2 as the main line (--workload c2): explicit controls from trim states."""
+    from aircraft_b200.workloads import trim_states
+    H = H_ROLL
+    xs, _ = trim_states(ac, per_gpu, seed=rank)
+    x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
+    U = device_control_sequences(torch, per_gpu, H, seed=100 + rank, device=dev)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+    ms_roll = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", return_final=False, cost=True), K, W, flush)
+    barrier()
     if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+        t = torch.tensor([ms_roll], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_roll = float(t.item())
+    x0_h = torch.empty((13, per_gpu), dtype=torch.float32).pin_memory(); x0_h.copy_(x0)
+    U_h = torch.empty((H, 7, per_gpu), dtype=torch.float32).pin_memory(); U_h.copy_(U)
+    x0_np, U_np = x0_h.numpy(), U_h.numpy()
+    for _ in range(2):
+        ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
+    t0 = time.perf_counter()
+    Ke = max(3, min(K, 10))
+    for _ in range(Ke):
+        ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
+    el = time.perf_counter() - t0
+    tfl = per_gpu * H * F_STEP / (ms_roll * 1e-3) / 1e12
+    return {
+        "metric": "surrogate RK4 state-steps/s", "value": per_gpu * world * H / (ms_roll * 1e-3),
+        "unit": "state-steps/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_roll,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config("c2", per_gpu, world),
+        "e2e": {"value": per_gpu * world * H * Ke / el, "unit": "state-steps/s",
+                "h2d_bytes_per_step": x0_np.nbytes + U_np.nbytes, "d2h_bytes_per_step": 4 * per_gpu, "steps": Ke,
+                "path": "airc_rollout_host (C ABI, pinned host buffers)"},
+        "gpu_launches": K,
+        "roofline": rollout_roofline("rollout_kernel<cost>", tfl, fp32_peak(ac), per_gpu * H, ms_roll, ms_roll),
+    }
 
 
 def measured_peaks():
@@ -426,6 +511,30 @@ def side_measurements(torch, ac, dev, rank, args):
     peaks, peak_src = measured_peaks()
     flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)   # 256 MB > 126 MB L2
     K = max(5, min(args.steps, 20))
+
+    # config 4 shard with EXPLICIT control tensors (the form a caller with its own sequences uses)
+    if args.workload == "c4":
+        n4 = args.per_gpu or C4_TOTAL // C4_GPUS
+        x1 = make_states(1, seed=4, level=True)
+        x0 = torch.tensor(x1.T, dtype=torch.float32, device=dev).expand(13, n4).contiguous()
+        U = device_control_sequences(torch, n4, H_ROLL, seed=100 + rank, device=dev)
+        ms = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", return_final=False, cost=True), K, 3, None)
+        x0_h = torch.empty((13, n4), dtype=torch.float32).pin_memory(); x0_h.copy_(x0)
+        U_h = torch.empty((H_ROLL, 7, n4), dtype=torch.float32).pin_memory(); U_h.copy_(U)
+        x0_np, U_np = x0_h.numpy(), U_h.numpy()
+        ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
+        t0 = time.perf_counter()
+        for _ in range(3):
+            ac.rollout(x0_np, U_np, DT, layout="soa", return_final=False, cost=True)
+        el = (time.perf_counter() - t0) / 3
+        out["c4_explicit"] = {"workload": f"config 4 shard with explicit control tensors: {n4} x {H_ROLL}, U[H,7,B] = "
+                                          f"{U_np.nbytes / 1e6:.0f} MB per launch (larger than L2)",
+                              "value": n4 * H_ROLL / (ms * 1e-3), "unit": "state-steps/s", "ms_per_launch": ms,
+                              "tflops": n4 * H_ROLL * F_STEP / (ms * 1e-3) / 1e12,
+                              "e2e": {"value": n4 * H_ROLL / el, "unit": "state-steps/s",
+                                      "h2d_bytes_per_step": x0_np.nbytes + U_np.nbytes, "d2h_bytes_per_step": 4 * n4,
+                                      "path": "airc_rollout_host (PCIe-bound: the control tensor crosses the bus)"}}
+        del x0, U, x0_h, U_h
 
     # config 2: 4096 rollouts x 200 from trim states (latency case)
     if args.workload != "c2":
