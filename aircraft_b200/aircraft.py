@@ -81,31 +81,44 @@ class RolloutResult:
     cost: Any = None           # [B]
 
 
-@dataclass
 class SweepRecord:
-    """The winner of a sampling sweep, decoded from the library's FP32 record."""
-    min_cost: Any = None         # 0-dim tensor / float
-    argmin: Any = None           # global trajectory index (0-dim int64 tensor / int)
-    trajectory: Any = None       # [H+1,13]
-    controls: Any = None         # [H,7]
-    cost: Any = None             # [B] when requested
-    raw: Any = None              # the undecoded record (what travels through the all-gather)
-    workspace: Any = None        # device scratch, reusable by the next sweep of the same size
+    """The winner of a sampling sweep: views into the library's FP32 record
+    [min cost, orderable cost bits, global arg-min (2 words), trajectory [H+1,13], controls [H,7]].
+    Nothing is computed or synchronised until a field is read."""
+
+    def __init__(self, raw, H: int, cost=None, workspace=None):
+        self.raw = raw                  # the undecoded record (what travels through the all-gather)
+        self.H = int(H)
+        self.cost = cost                # [B] when requested
+        self.workspace = workspace      # device scratch, reusable by the next sweep of the same size
+
+    @property
+    def min_cost(self):
+        return self.raw[0] if _is_torch(self.raw) else float(self.raw[0])
+
+    @property
+    def argmin(self):
+        """global trajectory index (0-dim int64 tensor, or int for host records)"""
+        if _is_torch(self.raw):
+            idx = self.raw[2:4].view(torch.int32).to(torch.int64)
+            return (idx[0] & 0xFFFFFFFF) | (idx[1] << 32)
+        idx = self.raw[2:4].view(np.uint32)
+        return int(idx[0]) | (int(idx[1]) << 32)
+
+    @property
+    def trajectory(self):
+        hdr, nt = _cabi.SWEEP_RECORD_HEADER, 13 * (self.H + 1)
+        return self.raw[hdr:hdr + nt].reshape(self.H + 1, 13)
+
+    @property
+    def controls(self):
+        hdr, nt = _cabi.SWEEP_RECORD_HEADER, 13 * (self.H + 1)
+        return self.raw[hdr + nt:hdr + nt + 7 * self.H].reshape(self.H, 7)
 
 
 def decode_record(raw, H: int, cost=None) -> SweepRecord:
     """Views into a record [4 + 13(H+1) + 7H] (torch tensor on any device, or numpy)."""
-    hdr = _cabi.SWEEP_RECORD_HEADER
-    nt = 13 * (H + 1)
-    if _is_torch(raw):
-        idx = raw[2:4].view(torch.int32).to(torch.int64)
-        gidx = (idx[0] & 0xFFFFFFFF) | (idx[1] << 32)
-        return SweepRecord(raw[0], gidx, raw[hdr:hdr + nt].view(H + 1, 13),
-                           raw[hdr + nt:hdr + nt + 7 * H].view(H, 7), cost, raw)
-    idx = raw[2:4].view(np.uint32)
-    gidx = int(idx[0]) | (int(idx[1]) << 32)
-    return SweepRecord(float(raw[0]), gidx, raw[hdr:hdr + nt].reshape(H + 1, 13),
-                       raw[hdr + nt:hdr + nt + 7 * H].reshape(H, 7), cost, raw)
+    return SweepRecord(raw, H, cost)
 
 
 def _check(rc: int, lib, what: str):

@@ -160,7 +160,7 @@ def sweep_sampled(aircraft, x0, U_nom, dt: float, total: int, *, sampler=None, c
         on_local()          # e.g. a CUDA event that separates the local kernels from the exchange
     if world == 1:
         return local
-    H = local.controls.shape[0]
+    H = local.H
     allrec = torch.empty((world, local.raw.numel()), dtype=torch.float32, device=local.raw.device)
     dist.all_gather_into_tensor(allrec, local.raw.reshape(1, -1), group=group)
     best = aircraft.select_record(allrec) if allrec.is_cuda else select_record_torch(allrec)
