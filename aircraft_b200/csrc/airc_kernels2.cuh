@@ -60,9 +60,10 @@ AIRC_D float rollout_cost_finish(const CostConst& cc, float px, float py, float 
 #ifndef AIRC_R2_MINBLOCKS
 #define AIRC_R2_MINBLOCKS 3
 #endif
-// Register budget: 144 registers = 14 warps/SM = 132 608 resident trajectories, so that the
-// 125 000-trajectory shard of BASELINE config 4 is ONE wave (at 152+ registers it is 1.1 waves and
-// the second, nearly empty wave costs as much as the first; profiles/r1_variants_packed.txt).
+// Register budget: <= 168 registers = 3 warps per SM sub-partition (the register file is per
+// sub-partition: 16384 / (32 x regs)), i.e. 3 blocks of 128 threads per SM.  144 registers do NOT give
+// 14 warps/SM, and 128 registers spill (profiles/r1_variants_packed.txt).  AIRC_R2_MAXNREG is the
+// experiment knob that established this.
 #ifdef AIRC_R2_MAXNREG
 #define AIRC_R2_BOUNDS __maxnreg__(AIRC_R2_MAXNREG)
 #else
@@ -112,9 +113,10 @@ rollout2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ Unit
       }
 #pragma unroll
       for (int i = 0; i < 7; ++i) up[i] = un[i];
-      sum_v2 = add2(sum_v2, body_speed2_2(P, s));
     }
-    state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0);
+    F2 speed2;
+    state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0, speed2);
+    if (COST) sum_v2 = add2(sum_v2, speed2);
     if (TRAJ) {
       store_half<false>(X0 + (long long)(k + 1) * a.X_sk, a.X_sc, s);
       if (live1) store_half<true>(X1 + (long long)(k + 1) * a.X_sk, a.X_sc, s);

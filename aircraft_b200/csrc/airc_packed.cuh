@@ -79,10 +79,10 @@ AIRC_HD F2 atan2_2(const F2& y, const F2& x) {
   const bool glo = ay.lo > ax.lo, ghi = ay.hi > ax.hi;
   const F2 mx{sel(glo, ay.lo, ax.lo), sel(ghi, ay.hi, ax.hi)};
   const F2 mn{sel(glo, ax.lo, ay.lo), sel(ghi, ax.hi, ay.hi)};
-  // t = mn/mx with a residual correction (~1 ulp); 0/0 -> t = 0
-  const F2 r = rcp2_nr(F2{mx.lo == 0.0f ? 1.0f : mx.lo, mx.hi == 0.0f ? 1.0f : mx.hi});
+  // t = mn/mx: MUFU.RCP (1 ulp) + a residual correction of the quotient (~1 ulp); 0/0 -> t = 0
+  const F2 r{fast_rcp(mx.lo == 0.0f ? 1.0f : mx.lo), fast_rcp(mx.hi == 0.0f ? 1.0f : mx.hi)};
   F2 t = mul2(mn, r);
-  t = fma2(fma2(neg2(t), mx, mn), r, t);
+  t = fma2(fma2(neg2(t), mx, mn), r, t);      // one residual step on the quotient: no Newton step on r needed
   const F2 s = mul2(t, t);
   F2 q = bc2(-2.447031215e-03f);
   q = fma2(q, s, bc2(1.375028427e-02f));
@@ -150,6 +150,10 @@ AIRC_HD float sign1(float x) { return (x > 0.0f) ? 1.0f : ((x < 0.0f) ? -1.0f : 
 #define AIRC_NN_UNROLL 16
 #endif
 constexpr int kNNUnroll = AIRC_NN_UNROLL;
+// (Tried and rejected, profiles/r1_variants_packed.txt: parking the control part of the hidden
+// pre-activations in shared memory once per step -- 10 % fewer FMAs but 20 % slower, LDS competes with
+// MUFU for the MIO queue; sharing one reciprocal between two units of a trajectory -- 2 % slower, the FMA
+// pipe, not the XU pipe, is the limiter.)
 // the surrogate for two trajectories: one hidden unit per 11 packed FMAs, weights broadcast
 AIRC_HD void surrogate2(const UnitNet& net, const F2& qbar, const F2& alpha, const F2& beta,
                         const Ctl2& c, F2 C[6]) {
@@ -175,7 +179,7 @@ AIRC_HD void surrogate2(const UnitNet& net, const F2& qbar, const F2& alpha, con
 
 // f(x,u) for two trajectories (p_dot = v is handled by the caller).  base.py:385-406.
 AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const F2 q[4],
-                     const F2 w[3], const Ctl2& c, F2 vdot[3], F2 qdot[4], F2 wdot[3]) {
+                     const F2 w[3], const Ctl2& c, F2 vdot[3], F2 qdot[4], F2 wdot[3], F2& vb2_out) {
   F2 M[9], n2;
   rot_matrix2(q, M, n2);
   const F2 inv_n2 = rcp2_nr(n2);
@@ -190,6 +194,7 @@ AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const
   }
   const F2 xz2 = fma2(vb[2], vb[2], mul2(vb[0], vb[0]));
   const F2 vb2 = fma2(vb[1], vb[1], xz2);
+  vb2_out = vb2;
   const F2 qbar = muls(0.6125f, vb2);                         // base.py:240
   const F2 xa = adds(vb[0], P.eps);
   const F2 alpha = atan2_2(vb[2], xa);                        // base.py:176
@@ -254,7 +259,9 @@ AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const
 
 // ---------------------------------------------------------------- RK4, normalise, loss pieces
 // state_step for two trajectories, base.py:408-446 (all 13 components additively).
-AIRC_HD void rk4_step2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float h) {
+// speed2 receives |v_b(x)|^2 of the step's FIRST stage, i.e. of the node itself: the loss's speed term
+// (control.py:63-64, aircraft.v_frd_rel on every node) costs nothing extra.
+AIRC_HD void rk4_step2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float h, F2& speed2) {
   const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
   F2 sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
 #pragma unroll
@@ -265,8 +272,9 @@ AIRC_HD void rk4_step2(const DevConst& P, const UnitNet& net, State2& x, const C
   for (int stage = 0; stage < 4; ++stage) {
     const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
     const float cn = (stage == 2) ? h : hh;
-    F2 kv[3], kq[4], kw[3];
-    f_eval2(P, net, sv, sq, sw, c, kv, kq, kw);
+    F2 kv[3], kq[4], kw[3], vb2;
+    f_eval2(P, net, sv, sq, sw, c, kv, kq, kw, vb2);
+    if (stage == 0) speed2 = vb2;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       ap[i] = fmas(wgt, sv[i], ap[i]);
@@ -300,10 +308,13 @@ AIRC_HD void normalise_q2(State2& x) {          // base.py:443-444, 473-474
 }
 
 // Phi(x,u,dt), base.py:450-480
+// speed2: |v_b|^2 at the node x (before the update), a by-product of the first RK4 stage
 AIRC_HD void state_update2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float dt,
-                           int substeps, bool normalise) {
+                           int substeps, bool normalise, F2& speed2) {
   const float h = (substeps == 1) ? dt : dt / (float)substeps;
-  for (int s = 0; s < substeps; ++s) rk4_step2(P, net, x, c, h);
+  F2 sp2;
+  rk4_step2(P, net, x, c, h, speed2);
+  for (int s = 1; s < substeps; ++s) rk4_step2(P, net, x, c, h, sp2);
   if (normalise) normalise_q2(x);
 }
 

@@ -1,15 +1,15 @@
-// airc_sweep2.cuh -- the sampling sweep on the packed arithmetic with TIME-SLICED PERSISTENT WARPS.
+// airc_sweep2.cuh -- the sampling sweep on the packed arithmetic, TIME-SLICED over the horizon.
 //
 // Why: a trajectory needs ~72 registers of live state per stage, so one SM holds at most 12 warps x
 // 64 trajectories; a B200 holds W = 148 x 12 warps = 113 664 trajectories at once.  BASELINE config
 // 4's shard (125 000) is 1.1 "waves": launched plainly, the 11 336 left-over trajectories run
 // almost alone for a whole horizon and cost as much as the full first wave (2.96 ms instead of
-// 2.2 ms x 1.1).  Here the horizon is cut into S segments and the (segment, group) tasks are handed
-// out segment-major from an atomic counter to W resident warps; a group's state round-trips through
+// 2.2 ms x 1.1).  Here the horizon is cut into S segments and the (segment, group) tasks are blocks in
+// segment-major index order, which the hardware hands to warp slots as they free up; a group's state round-trips through
 // a 23-float slice record in HBM between segments (traffic ~1 % of the kernel's time).  All warps
 // stay busy until the very end: makespan ~ ceil(G S / W)/S waves instead of ceil(G / W).
-// A task (s, g) waits on flag[g] >= s; its predecessor (s-1, g) was dequeued earlier, so it is
-// running on a resident warp or done -- no deadlock whatever the residency.
+// A task (s, g) waits on flag[g] >= s; its predecessor (s-1, g) has a lower block index, was dispatched
+// earlier, and is therefore running on a resident warp or done -- no deadlock whatever the residency.
 #pragma once
 #include "airc_kernels2.cuh"
 #include "airc_sweep.cuh"
@@ -151,9 +151,10 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
       }
 #pragma unroll
       for (int c = 0; c < 4; ++c) up[c] = un[c];
-      sum_v2 = add2(sum_v2, body_speed2_2(P, s));
       const Ctl2 c{un[0], un[1], un[2], un[3]};
-      state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0);
+      F2 speed2;
+      state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0, speed2);
+      sum_v2 = add2(sum_v2, speed2);
     }
     if (k1 < a.H) {
       // hand the group over to whoever picks up (seg+1, g)
@@ -247,7 +248,8 @@ __global__ void sweep_winner2_kernel(const __grid_constant__ DevConst P, const _
 #pragma unroll
     for (int c = 3; c < 6; ++c) uo[c] = a.Unom[k * 7 + c];
     const Ctl2 c{bc2(un[0]), bc2(un[1]), bc2(un[2]), bc2(un[3])};
-    state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0);
+    F2 speed2;
+    state_update2(P, N, s, c, a.dt, a.substeps, a.normalise != 0, speed2);
     store_half<false>(traj + 13 * (k + 1), 1, s);
   }
 }

@@ -222,6 +222,8 @@ int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
                         const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                         int layout, float* x_next, float* A, float* Bm);
 
+/* airc_sweep with HOST x0 [13], U_nom [H][7], cost (optional, [B]) and record: copies in, runs the three
+ * kernels on the handle's stream with handle-owned workspace, copies the record out, synchronises. */
 int airc_sweep_host(AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
                     int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
                     float* cost, float* record);
