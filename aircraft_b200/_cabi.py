@@ -54,6 +54,10 @@ class AircSweepParams(C.Structure):
 
 
 SWEEP_RECORD_HEADER = 4
+NDIAG = 22
+DIAG_SLICES = {"v_frd_rel": slice(0, 3), "airspeed": 3, "alpha": 4, "beta": 5, "qbar": 6,
+               "coefficients": slice(7, 13), "forces_frd": slice(13, 16), "moments_frd": slice(16, 19),
+               "phi": 19, "theta": 20, "psi": 21}
 
 assert C.sizeof(AircNNBlob) == 860 * 4
 assert C.sizeof(AircSweepParams) == 88
@@ -72,11 +76,15 @@ PROTOTYPES = {
     "airc_destroy": (C.c_int, [_vp]),
     "airc_last_error": (C.c_char_p, [_vp]),
     "airc_state_derivative": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp]),
+    "airc_diagnostics": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp]),
+    "airc_diagnostics_host": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),
     "airc_state_update": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp]),
     "airc_rollout": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _i32, _vp, _vp, _vp,
                                _CP, _vp]),
     "airc_linearize": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                  _vp]),
+    "airc_linearize_dt": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
+                                    _vp, _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "airc_sweep_record_floats": (C.c_int64, [_i32]),
     "airc_sweep_workspace_bytes": (C.c_size_t, [_i64, _i32, _i32]),
@@ -92,6 +100,8 @@ PROTOTYPES = {
                                     _vp, _CP]),
     "airc_linearize_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp,
                                       _vp]),
+    "airc_linearize_dt_host": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp,
+                                         _vp, _vp]),
 }
 
 _lib = None

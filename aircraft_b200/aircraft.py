@@ -445,7 +445,7 @@ class Aircraft:
 
     def linearize(self, x, u, dt, *, substeps: Optional[int] = None,
                   normalise: Optional[bool] = None, layout: str = "aos",
-                  want_next: bool = True):
+                  want_next: bool = True, want_dt: bool = False):
         """(x_next, A = dPhi/dx, B = dPhi/du) at every node by forward-mode tangents: what the
         reference obtains from ca.jacobian(state_update, x|u) (control/aircraft.py:85-95,
         base.py:51-52, main/stability/stability.py:48-54) and IPOPT from the defect constraints
@@ -453,6 +453,10 @@ class Aircraft:
 
         layout 'aos': x[...,13], u[...,7] -> x_next[...,13], A[...,13,13], B[...,13,7]
         layout 'soa': x[13,N],  u[7,N]   -> x_next[13,N],  A[13,13,N],  B[13,7,N]
+
+        want_dt=True appends dPhi/d(dt) ([...,13] / [13,N]) to the returned tuple: the step-size
+        column of the variable-dt / time='progress' transcriptions (control/base.py:255-286),
+        carried in a spare tangent slot of the same kernel launch.
         """
         if layout not in ("aos", "soa"):
             raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
@@ -480,19 +484,88 @@ class Aircraft:
             (lambda s: np.empty(s, np.float32))
         xn = mk(shp_x) if want_next else None
         A, Bm = mk(shp_A), mk(shp_B)
+        Dt = mk(shp_x) if want_dt else None
         lib, h = self._lib, self.handle
         lay = LAYOUT_SOA if soa else LAYOUT_AOS
         ns, fl = self._substeps(substeps), self._flags(normalise)
         if on_dev:
-            _check(lib.airc_linearize(h, xd.data_ptr(), ud.data_ptr(), dts, self._ptr(dtn), n, ns, fl,
-                                      lay, self._ptr(xn), A.data_ptr(), Bm.data_ptr(), self._stream()),
-                   lib, "airc_linearize")
+            _check(lib.airc_linearize_dt(h, xd.data_ptr(), ud.data_ptr(), dts, self._ptr(dtn), n, ns, fl,
+                                         lay, self._ptr(xn), A.data_ptr(), Bm.data_ptr(), self._ptr(Dt),
+                                         self._stream()),
+                   lib, "airc_linearize_dt")
         else:
-            _check(lib.airc_linearize_host(h, xd.ctypes.data, ud.ctypes.data, dts, self._ptr(dtn), n,
-                                           ns, fl, lay, self._ptr(xn), A.ctypes.data, Bm.ctypes.data),
-                   lib, "airc_linearize_host")
-            xn, A, Bm = (None if a is None else self._like(a, x) for a in (xn, A, Bm))
-        return xn, A, Bm
+            _check(lib.airc_linearize_dt_host(h, xd.ctypes.data, ud.ctypes.data, dts, self._ptr(dtn), n,
+                                              ns, fl, lay, self._ptr(xn), A.ctypes.data, Bm.ctypes.data,
+                                              self._ptr(Dt)),
+                   lib, "airc_linearize_dt_host")
+            xn, A, Bm, Dt = (None if a is None else self._like(a, x) for a in (xn, A, Bm, Dt))
+        return (xn, A, Bm, Dt) if want_dt else (xn, A, Bm)
+
+    # ------------------------------------------------------------------ side functions (diagnostics)
+    def diagnostics(self, x, u):
+        """All side functions of the reference's dynamics object in one pass per node (column call
+        shape like state_update): dict of v_frd_rel[3,N], airspeed[N], alpha[N], beta[N], qbar[N],
+        coefficients[6,N], forces_frd[3,N], moments_frd[3,N], phi[N], theta[N], psi[N]
+        (base.py:147-241,253-278; aircraft.py:255-330)."""
+        x2, u2, n, squeeze = self._columns(x, u)
+        lib, h = self._lib, self.handle
+        if self._on_device(x2, u2):
+            xd, ud = self._dev32(x2, "x"), self._dev32(u2, "u")
+            out = torch.empty((_cabi.NDIAG, n), dtype=torch.float32, device=xd.device)
+            _check(lib.airc_diagnostics(h, xd.data_ptr(), ud.data_ptr(), n, LAYOUT_SOA, out.data_ptr(),
+                                        self._stream()), lib, "airc_diagnostics")
+        else:
+            xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
+            out = np.empty((_cabi.NDIAG, n), np.float32)
+            _check(lib.airc_diagnostics_host(h, xh.ctypes.data, uh.ctypes.data, n, LAYOUT_SOA,
+                                             out.ctypes.data), lib, "airc_diagnostics_host")
+            out = self._like(out, x)
+        res = {}
+        for name, sl in _cabi.DIAG_SLICES.items():
+            v = out[sl]
+            res[name] = v[..., 0] if squeeze else v
+        return res
+
+    def _diag(self, name, x, u=None):
+        if u is None:      # phi/theta/psi are functions of the state alone (base.py:179-197)
+            xs = x if hasattr(x, "shape") else np.asarray(x)
+            n = xs.shape[1] if len(xs.shape) == 2 else None
+            u = torch.zeros((NU,) if n is None else (NU, n), device=x.device) if _is_torch(x) else \
+                np.zeros((NU,) if n is None else (NU, n))
+        return self.diagnostics(x, u)[name]
+
+    def v_frd_rel(self, x, u):
+        return self._diag("v_frd_rel", x, u)
+
+    def airspeed(self, x, u):
+        return self._diag("airspeed", x, u)
+
+    def alpha(self, x, u):
+        return self._diag("alpha", x, u)
+
+    def beta(self, x, u):
+        return self._diag("beta", x, u)
+
+    def qbar(self, x, u):
+        return self._diag("qbar", x, u)
+
+    def coefficients(self, x, u):
+        return self._diag("coefficients", x, u)
+
+    def forces_frd(self, x, u):
+        return self._diag("forces_frd", x, u)
+
+    def moments_frd(self, x, u):
+        return self._diag("moments_frd", x, u)
+
+    def phi(self, x):
+        return self._diag("phi", x)
+
+    def theta(self, x):
+        return self._diag("theta", x)
+
+    def psi(self, x):
+        return self._diag("psi", x)
 
     # ------------------------------------------------------------------ sampling-MPC sweep
     def sweep(self, x0, U_nom, dt: float, B: int, *, sampler=None, cost=True,

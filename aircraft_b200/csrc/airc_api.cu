@@ -129,6 +129,20 @@ int airc_state_derivative(const AircHandle* h, const float* x, const float* u, i
   return check_launch();
 }
 
+int airc_diagnostics(const AircHandle* h, const float* x, const float* u, int64_t n, int layout,
+                     float* out, void* stream) {
+  if (!h || !x || !u || !out || n < 0 || (layout != 0 && layout != 1))
+    return fail(AIRC_EINVAL, "airc_diagnostics: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(out, n, AIRC_NDIAG, layout), nullptr, 0.f, n, 1, 0};
+  static_assert(AIRC_NDIAG == NDIAG, "header and kernel disagree on the diagnostics record");
+  const int bs = 128;
+  diagnostics_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  return check_launch();
+}
+
 int airc_state_update(const AircHandle* h, const float* x, const float* u, float dt,
                       const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                       int layout, float* x_next, void* stream) {
@@ -198,9 +212,9 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
   return check_launch();
 }
 
-int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt,
-                   const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
-                   float* x_next, float* A, float* Bm, void* stream) {
+static int linearize_impl(const AircHandle* h, const float* x, const float* u, float dt,
+                          const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                          float* x_next, float* A, float* Bm, float* Dt, void* stream) {
   if (!h || !x || !u || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_linearize: bad argument%s", "");
@@ -212,7 +226,7 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
   a.x = view(x, n, 13, layout);
   a.u = view(u, n, 7, layout);
   a.xn = viewW(x_next, n, 13, layout);
-  a.A = A; a.Bm = Bm;
+  a.A = A; a.Bm = Bm; a.Dt = Dt;
   if (layout == AIRC_LAYOUT_SOA) { a.A_sn = 1; a.A_se = n; a.B_sn = 1; a.B_se = n; }
   else { a.A_sn = 169; a.A_se = 1; a.B_sn = 91; a.B_se = 1; }
   a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
@@ -228,6 +242,21 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
   else linearize_coop_kernel<8, false><<<grid, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
 #endif
   return check_launch();
+}
+
+int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt,
+                   const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                   float* x_next, float* A, float* Bm, void* stream) {
+  return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, nullptr, stream);
+}
+
+int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                      float* x_next, float* A, float* Bm, float* dPhi_ddt, void* stream) {
+#ifdef AIRC_LIN_V1
+  if (dPhi_ddt) return fail(AIRC_EINVAL, "airc_linearize_dt: not available in the AIRC_LIN_V1 build%s", "");
+#endif
+  return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt, stream);
 }
 
 int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
@@ -494,6 +523,25 @@ int airc_state_derivative_host(AircHandle* h, const float* x, const float* u, in
   return AIRC_OK;
 }
 
+int airc_diagnostics_host(AircHandle* h, const float* x, const float* u, int64_t n, int layout, float* out) {
+  if (!h || !x || !u || !out || n < 0) return fail(AIRC_EINVAL, "airc_diagnostics_host: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t bx = al(13 * n), bu = al(7 * n), bo = al((size_t)AIRC_NDIAG * n);
+  int rc = ensure_scratch(h, bx + bu + bo);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float *dx = (float*)base, *du = (float*)(base + bx), *dn = (float*)(base + bx + bu);
+  CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_diagnostics(h, dx, du, n, layout, dn, h->hstream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(out, dn, (size_t)AIRC_NDIAG * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
+}
+
 int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt,
                            const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                            int layout, float* x_next) {
@@ -547,16 +595,16 @@ int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, 
   return AIRC_OK;
 }
 
-int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
-                        const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
-                        int layout, float* x_next, float* A, float* Bm) {
+static int linearize_host_impl(AircHandle* h, const float* x, const float* u, float dt,
+                               const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                               int layout, float* x_next, float* A, float* Bm, float* Dt) {
   if (!h || !x || !u || n < 0) return fail(AIRC_EINVAL, "airc_linearize_host: bad argument%s", "");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   const size_t bx = al(13 * n), bu = al(7 * n), bA = A ? al(169 * n) : 0, bB = Bm ? al(91 * n) : 0;
-  const size_t bd = dt_per_node ? al(n) : 0;
-  int rc = ensure_scratch(h, 2 * bx + bu + bA + bB + bd);
+  const size_t bd = dt_per_node ? al(n) : 0, bT = Dt ? al(13 * n) : 0;
+  int rc = ensure_scratch(h, 2 * bx + bu + bA + bB + bd + bT);
   if (rc) return rc;
   char* base = (char*)h->scratch;
   float* dx = (float*)base;
@@ -565,16 +613,30 @@ int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
   float* dA = A ? (float*)(base + 2 * bx + bu) : nullptr;
   float* dB = Bm ? (float*)(base + 2 * bx + bu + bA) : nullptr;
   float* ddt = dt_per_node ? (float*)(base + 2 * bx + bu + bA + bB) : nullptr;
+  float* dT = Dt ? (float*)(base + 2 * bx + bu + bA + bB + bd) : nullptr;
   if (ddt) CUDA_TRY(cudaMemcpyAsync(ddt, dt_per_node, n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
   CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
   CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
-  rc = airc_linearize(h, dx, du, dt, ddt, n, substeps, flags, layout, dn, dA, dB, h->hstream);
+  rc = airc_linearize_dt(h, dx, du, dt, ddt, n, substeps, flags, layout, dn, dA, dB, dT, h->hstream);
   if (rc) return rc;
   if (x_next) CUDA_TRY(cudaMemcpyAsync(x_next, dn, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   if (A) CUDA_TRY(cudaMemcpyAsync(A, dA, 169 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   if (Bm) CUDA_TRY(cudaMemcpyAsync(Bm, dB, 91 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (Dt) CUDA_TRY(cudaMemcpyAsync(Dt, dT, 13 * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
   CUDA_TRY(cudaStreamSynchronize(h->hstream));
   return AIRC_OK;
+}
+
+int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
+                        const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                        int layout, float* x_next, float* A, float* Bm) {
+  return linearize_host_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, nullptr);
+}
+
+int airc_linearize_dt_host(AircHandle* h, const float* x, const float* u, float dt,
+                           const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                           int layout, float* x_next, float* A, float* Bm, float* dPhi_ddt) {
+  return linearize_host_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt);
 }
 
 int airc_sweep_host(AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,

@@ -91,12 +91,16 @@ template <class T>
 struct TangentT {
   T p[3], v[3], q[4], w[3];
   CtlT<T> dc;
+  T ddt;   // d(dt) along this column: 1 for the dPhi/d(dt) column (control/base.py:276, time='progress'), else 0
 };
 
 // One RK4 step of the primal with ONE tangent of type T alongside (base.py:408-446 and its
 // forward-mode derivative).  f does not read p, so d(p_dot) = dv.
+// dh = d(h)/d(dt) * D.ddt (h = dt/substeps): the step-size direction of this column.  The stage
+// states X_{i+1} = x + c_i h k_i and the update x+ = x + h/6 sum w_i k_i depend on h explicitly.
 template <class T, class Net>
-AIRC_HD void rk4_step_lin(const DevConst& P, const Net& net, State& x, const Ctl& c, float h, TangentT<T>& D) {
+AIRC_HD void rk4_step_lin(const DevConst& P, const Net& net, State& x, const Ctl& c, float h, TangentT<T>& D,
+                          const T& dh) {
   const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
   float sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
   T tv[3], tq[4], tw[3], bp[3], bv[3], bq[4], bw[3];
@@ -112,6 +116,7 @@ AIRC_HD void rk4_step_lin(const DevConst& P, const Net& net, State& x, const Ctl
   for (int stage = 0; stage < 4; ++stage) {
     const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
     const float cn = (stage == 2) ? h : hh;
+    const T dcn = tmul((stage == 2) ? 1.0f : 0.5f, dh);      // d(c_i h) along this column
     float kv[3], kq[4], kw[3], J[6][5];
     Stage s;
     f_eval_net<true>(P, net, sv, sq, sw, c, kv, kq, kw, s, J);
@@ -122,8 +127,8 @@ AIRC_HD void rk4_step_lin(const DevConst& P, const Net& net, State& x, const Ctl
       bp[i] = tfma(wgt, tv[i], bp[i]);
       bv[i] = tfma(wgt, dkv[i], bv[i]);
       bw[i] = tfma(wgt, dkw[i], bw[i]);
-      tv[i] = tfma(cn, dkv[i], D.v[i]);
-      tw[i] = tfma(cn, dkw[i], D.w[i]);
+      tv[i] = tfma(kv[i], dcn, tfma(cn, dkv[i], D.v[i]));
+      tw[i] = tfma(kw[i], dcn, tfma(cn, dkw[i], D.w[i]));
       ap[i] = fmaf(wgt, sv[i], ap[i]);
       av[i] = fmaf(wgt, kv[i], av[i]);
       aw[i] = fmaf(wgt, kw[i], aw[i]);
@@ -133,24 +138,25 @@ AIRC_HD void rk4_step_lin(const DevConst& P, const Net& net, State& x, const Ctl
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       bq[i] = tfma(wgt, dkq[i], bq[i]);
-      tq[i] = tfma(cn, dkq[i], D.q[i]);
+      tq[i] = tfma(kq[i], dcn, tfma(cn, dkq[i], D.q[i]));
       aq[i] = fmaf(wgt, kq[i], aq[i]);
       sq[i] = fmaf(cn, kq[i], x.q[i]);
     }
   }
+  const T dh6 = tmul(1.0f / 6.0f, dh);                       // d(h/6) along this column
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
+    D.p[i] = tfma(ap[i], dh6, tfma(h6, bp[i], D.p[i]));
+    D.v[i] = tfma(av[i], dh6, tfma(h6, bv[i], D.v[i]));
+    D.w[i] = tfma(aw[i], dh6, tfma(h6, bw[i], D.w[i]));
     x.p[i] = fmaf(h6, ap[i], x.p[i]);
     x.v[i] = fmaf(h6, av[i], x.v[i]);
     x.w[i] = fmaf(h6, aw[i], x.w[i]);
-    D.p[i] = tfma(h6, bp[i], D.p[i]);
-    D.v[i] = tfma(h6, bv[i], D.v[i]);
-    D.w[i] = tfma(h6, bw[i], D.w[i]);
   }
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
+    D.q[i] = tfma(aq[i], dh6, tfma(h6, bq[i], D.q[i]));
     x.q[i] = fmaf(h6, aq[i], x.q[i]);
-    D.q[i] = tfma(h6, bq[i], D.q[i]);
   }
 }
 
@@ -171,7 +177,8 @@ template <class T, class Net>
 AIRC_HD void state_update_lin(const DevConst& P, const Net& net, State& x, const Ctl& c, float dt,
                               int substeps, bool normalise, TangentT<T>& D) {
   const float h = (substeps == 1) ? dt : dt / (float)substeps;
-  for (int s = 0; s < substeps; ++s) rk4_step_lin<T>(P, net, x, c, h, D);
+  const T dh = (substeps == 1) ? D.ddt : tmul(1.0f / (float)substeps, D.ddt);
+  for (int s = 0; s < substeps; ++s) rk4_step_lin<T>(P, net, x, c, h, D, dh);
   if (normalise) normalise_q_lin<T>(x, D);
 }
 

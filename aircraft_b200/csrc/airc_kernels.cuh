@@ -100,6 +100,48 @@ state_update_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   store_state(a.out, i, s);
 }
 
+// ------------------------------------------------------------------------------------ K0''  (diagnostics)
+// The side functions the reference exposes next to the dynamics and evaluates on every node for
+// envelope constraints, losses, logging and plots (control/aircraft.py:44-59,140-142,
+// main/control/control.py:63-64, plotting/plotting.py:349,363), in one pass per node:
+//   out[0:3]  v_frd_rel        base.py:147-162        out[7:13]  coefficients   aircraft.py:255-307
+//   out[3]    airspeed         base.py:164-170        out[13:16] forces_frd     aircraft.py:309-321
+//   out[4]    alpha            base.py:172-177        out[16:19] moments_frd    aircraft.py:323-330, base.py:253-278
+//   out[5]    beta             base.py:229-235        out[19:22] phi, theta, psi base.py:179-197
+//   out[6]    qbar             base.py:237-241
+constexpr int NDIAG = 22;
+__global__ void __launch_bounds__(128)
+diagnostics_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  State s;
+  load_state(a.x, i, s);
+  const Ctl c = load_ctl(a.u.base + i * a.u.sb, a.u.sc);
+  State d;
+  Stage st;
+  float J[6][5];
+  f_eval<false>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
+  float o[NDIAG];
+  const float vb2 = fmaf(st.vb[2], st.vb[2], fmaf(st.vb[1], st.vb[1], st.vb[0] * st.vb[0]));
+  float V, rV;
+  sqrt_rsqrt(vb2 + P.eps, V, rV);
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { o[k] = st.vb[k]; o[13 + k] = st.F[k]; }
+  o[3] = V; o[4] = st.alpha; o[5] = st.beta; o[6] = st.qbar;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) o[7 + k] = st.C[k];
+  o[16] = st.C[3] * (st.qbar * P.Sb) + (P.com[1] * st.F[2] - P.com[2] * st.F[1]);
+  o[17] = st.C[4] * (st.qbar * P.Sc) + (P.com[2] * st.F[0] - P.com[0] * st.F[2]);
+  o[18] = st.C[5] * (st.qbar * P.Sb) + (P.com[0] * st.F[1] - P.com[1] * st.F[0]);
+  const float x = s.q[0], y = s.q[1], z = s.q[2], w = s.q[3];
+  o[19] = atan2f(2.0f * (w * x + y * z), 1.0f - 2.0f * (x * x + y * y));
+  o[20] = asinf(2.0f * (w * y - z * x));
+  o[21] = atan2f(2.0f * (w * z + x * y), 1.0f - 2.0f * (y * y + z * z));
+  float* p = a.out.base + i * a.out.sb;
+#pragma unroll
+  for (int k = 0; k < NDIAG; ++k) p[k * a.out.sc] = o[k];
+}
+
 // ------------------------------------------------------------------------------------ K1
 struct CostConst {
   float goal0, goal1, vel_param, w_goal, w_du, neg_log2e_over_eps, w_height, w_speed_over_H,
@@ -211,6 +253,7 @@ struct LinArgs {
   long long A_sn, A_se;
   float* Bm;                 // optional; element (node, r, c) at Bm[node*B_sn + (r*7+c)*B_se]
   long long B_sn, B_se;
+  float* Dt;                 // optional dPhi/d(dt): SoA [13][n] / AoS [n][13]
   const float* dt_per_node;
   float dt;
   long long n;
@@ -295,7 +338,8 @@ linearize_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
 // L = 8 lanes per node, 4 nodes per warp.  Column slots 2*lane, 2*lane+1 (one packed tangent):
 //   slots 0..9   d/d(v, q, omega)      = A columns 3..12            (lanes 0..4)
 //   slots 10..13 d/d(aileron, elevator, rudder, flaps) = B columns 0,1,2,6   (lanes 5, 6)
-//   lane 7 carries no tangent work of its own: it writes x+ and the constant columns
+//   slot 14      d/d(dt)  (the step-size column of time='progress' mode, control/base.py:276)   (lane 7)
+//   lane 7 also writes x+ and the constant columns
 //   dPhi/dp = [I;0] and dPhi/d(thrust) = 0 (f does not read p; thrust is inert, aircraft.py:320).
 // The surrogate and its 6x5 Jacobian are shared: two hidden-unit pairs per lane, all-reduced by
 // shuffles (NetCoop).  The network lives in shared memory because each lane reads different pairs.
@@ -332,6 +376,7 @@ linearize_coop_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) D.q[i] = seed(3 + i);
   D.dc.da = seed(10); D.dc.de = seed(11); D.dc.dr = seed(12); D.dc.df = seed(13);
+  D.ddt = seed(14);
 
   const NetCoop<L> net{&snet, lane};
   state_update_lin<F2>(P, net, s, c, dt, a.substeps, a.normalise != 0, D);
@@ -362,6 +407,11 @@ linearize_coop_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
     }
   } else {
     if (a.xn.base) store_state(a.xn, node, s);
+    if (a.Dt) {
+      float* o = a.Dt + (SOA ? node : node * 13);
+#pragma unroll
+      for (int r = 0; r < 13; ++r) o[r * es] = col[r].lo;
+    }
     if (Ab) {
       float* o = Ab;
 #pragma unroll

@@ -118,6 +118,17 @@ const char* airc_last_error(const AircHandle* h);
 int airc_state_derivative(const AircHandle* h, const float* x, const float* u, int64_t n,
                           int layout, float* xdot, void* stream);
 
+/* The side functions of the dynamics object, all at once, for n nodes: replaces the ca.Functions
+ * v_frd_rel, airspeed, alpha, beta, qbar (base.py:147-177,229-241), coefficients (aircraft.py:255-307),
+ * forces_frd, moments_frd (aircraft.py:309-330, base.py:253-278) and phi, theta, psi (base.py:179-197) that the
+ * reference evaluates on every node for envelope constraints, losses, logging and plots
+ * (control/aircraft.py:44-59,140-142; main/control/control.py:63-64).
+ * out: [22][n] (SOA) or [n][22] (AOS):  0:3 v_frd_rel | 3 airspeed | 4 alpha | 5 beta | 6 qbar |
+ *      7:13 CX CY CZ Cl Cm Cn | 13:16 forces_frd | 16:19 moments_frd | 19:22 phi theta psi */
+#define AIRC_NDIAG 22
+int airc_diagnostics(const AircHandle* h, const float* x, const float* u, int64_t n, int layout,
+                     float* out, void* stream);
+
 /* Phi(x,u,dt): replaces ca.Function 'state_update' (base.py:476-480) for n independent
  * (x,u,dt) nodes.  dt_per_node may be NULL (then dt is used for all nodes). */
 int airc_state_update(const AircHandle* h, const float* x, const float* u, float dt,
@@ -144,6 +155,16 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
 int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt,
                    const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
                    float* x_next, float* A, float* Bm, void* stream);
+
+/* airc_linearize plus the step-size column dPhi/d(dt): the derivative the reference's time='progress'
+ * / variable-dt transcriptions take through ca.jacobian of the defect x[k+1] - Phi(x[k],u[k],dt[k])
+ * w.r.t. the dt decision variable (control/base.py:255-286, control/minimal.py time handling).
+ * It rides in the 15th tangent slot of the same kernel launch (no extra passes).
+ *   dPhi_ddt: SOA [13][n] / AOS [n][13], or NULL (then identical to airc_linearize).
+ * With substeps s the derivative is w.r.t. the whole-node dt (each substep sees d(dt/s) = 1/s).  */
+int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                      float* x_next, float* A, float* Bm, float* dPhi_ddt, void* stream);
 
 /* (min, argmin) of cost[B] by warp-shuffle + 64-bit atomicMin; ties go to the lower index.
  * out_min: 1 float, out_idx: 1 int64 (device). */
@@ -212,6 +233,7 @@ int airc_measure_fp32_peak(const AircHandle* h, int repeats, double* tflops, dou
  * synchronises.  Same semantics as the device-pointer versions. */
 int airc_state_derivative_host(AircHandle* h, const float* x, const float* u, int64_t n, int layout,
                                float* xdot);
+int airc_diagnostics_host(AircHandle* h, const float* x, const float* u, int64_t n, int layout, float* out);
 int airc_state_update_host(AircHandle* h, const float* x, const float* u, float dt,
                            const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                            int layout, float* x_next);
@@ -221,6 +243,9 @@ int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, 
 int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
                         const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                         int layout, float* x_next, float* A, float* Bm);
+int airc_linearize_dt_host(AircHandle* h, const float* x, const float* u, float dt,
+                           const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
+                           int layout, float* x_next, float* A, float* Bm, float* dPhi_ddt);
 
 /* airc_sweep with HOST x0 [13], U_nom [H][7], cost (optional, [B]) and record: copies in, runs the three
  * kernels on the handle's stream with handle-owned workspace, copies the record out, synchronises. */

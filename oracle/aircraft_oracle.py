@@ -162,6 +162,15 @@ class AircraftOracle:
         qbar = 0.5 * 1.225 * vb2
         return vb, airspeed, alpha, beta, qbar
 
+    # ---- Euler angles from the xyzw quaternion (base.py:179-197)
+    @staticmethod
+    def euler(x: torch.Tensor) -> torch.Tensor:
+        qx, qy, qz, qw = x[..., 6], x[..., 7], x[..., 8], x[..., 9]
+        phi = torch.atan2(2 * (qw * qx + qy * qz), 1 - 2 * (qx ** 2 + qy ** 2))
+        theta = torch.asin(2 * (qw * qy - qz * qx))
+        psi = torch.atan2(2 * (qw * qz + qx * qy), 1 - 2 * (qy ** 2 + qz ** 2))
+        return torch.stack([phi, theta, psi], dim=-1)
+
     # ---- coefficients (aircraft.py:255-307)
     def coefficients(self, x: torch.Tensor, u: torch.Tensor) -> torch.Tensor:
         vb, _, alpha, beta, qbar = self.aero_inputs(x)
@@ -274,7 +283,7 @@ class AircraftOracle:
 
     # ---- A = dPhi/dx, B = dPhi/du by forward AD (reference: ca.jacobian, control/aircraft.py:88,
     #      main/stability/stability.py:51, base.py:51-52)
-    def linearize(self, x, u, dt, substeps=None, normalise=None):
+    def linearize(self, x, u, dt, substeps=None, normalise=None, want_dt=False):
         x = torch.as_tensor(x, dtype=F64).reshape(-1, 13)
         u = torch.as_tensor(u, dtype=F64).reshape(-1, 7)
         dtt = torch.as_tensor(dt, dtype=F64).expand(x.shape[0]) if torch.as_tensor(dt).ndim == 0 \
@@ -283,6 +292,10 @@ class AircraftOracle:
         def phi(xi, ui, di):
             return self.state_update(xi, ui, di, substeps, normalise)
 
+        if want_dt:   # + dPhi/d(dt), the variable-step column (control/base.py:255-286)
+            jac = torch.func.vmap(torch.func.jacfwd(phi, argnums=(0, 1, 2)))
+            A, Bm, Dt = jac(x, u, dtt)
+            return phi(x, u, dtt), A, Bm, Dt
         jac = torch.func.vmap(torch.func.jacfwd(phi, argnums=(0, 1)))
         A, Bm = jac(x, u, dtt)
         return phi(x, u, dtt), A, Bm

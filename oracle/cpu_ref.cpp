@@ -266,6 +266,31 @@ int set_threads(int threads) {
 
 }  // namespace
 
+// A[n][13][13], Bm[n][13][7] by 20-direction forward mode; a 21st direction carries d/d(dt)
+// (the dt decision variable of the reference's variable-step transcriptions, control/base.py:255-286)
+template <int ND>
+static void linearize_nd(const AircParams* p, const AircNNBlob* nn, const double* x, const double* u,
+                         double dt, int64_t n, int substeps, uint32_t flags, double* xn, double* A,
+                         double* Bm, double* Dt, int threads) {
+  Model m; make_model(p, nn, m); set_threads(threads);
+  typedef Dual<ND> D;
+#pragma omp parallel for schedule(static)
+  for (int64_t i = 0; i < n; ++i) {
+    D s[13], c[7];
+    for (int k = 0; k < 13; ++k) { s[k] = D(x[13 * i + k]); s[k].d[k] = 1.0; }
+    for (int k = 0; k < 7; ++k) { c[k] = D(u[7 * i + k]); c[k].d[13 + k] = 1.0; }
+    D h(dt);
+    if (ND > 20) h.d[ND - 1] = 1.0;
+    phi<D>(m, s, c, h, substeps, flags & AIRC_FLAG_NORMALISE);
+    for (int r = 0; r < 13; ++r) {
+      if (xn) xn[13 * i + r] = s[r].v;
+      if (A) for (int k = 0; k < 13; ++k) A[(i * 13 + r) * 13 + k] = s[r].d[k];
+      if (Bm) for (int k = 0; k < 7; ++k) Bm[(i * 13 + r) * 7 + k] = s[r].d[13 + k];
+      if (ND > 20 && Dt) Dt[13 * i + r] = s[r].d[ND - 1];
+    }
+  }
+}
+
 extern "C" {
 
 int cpuref_max_threads(void) {
@@ -312,24 +337,16 @@ void cpuref_rollout(const AircParams* p, const AircNNBlob* nn, const double* x0,
   }
 }
 
-// A[n][13][13], Bm[n][13][7] by 20-direction forward mode
 void cpuref_linearize(const AircParams* p, const AircNNBlob* nn, const double* x, const double* u,
                       double dt, int64_t n, int substeps, uint32_t flags, double* xn, double* A,
                       double* Bm, int threads) {
-  Model m; make_model(p, nn, m); set_threads(threads);
-  typedef Dual<20> D;
-#pragma omp parallel for schedule(static)
-  for (int64_t i = 0; i < n; ++i) {
-    D s[13], c[7];
-    for (int k = 0; k < 13; ++k) { s[k] = D(x[13 * i + k]); s[k].d[k] = 1.0; }
-    for (int k = 0; k < 7; ++k) { c[k] = D(u[7 * i + k]); c[k].d[13 + k] = 1.0; }
-    phi<D>(m, s, c, D(dt), substeps, flags & AIRC_FLAG_NORMALISE);
-    for (int r = 0; r < 13; ++r) {
-      if (xn) xn[13 * i + r] = s[r].v;
-      if (A) for (int k = 0; k < 13; ++k) A[(i * 13 + r) * 13 + k] = s[r].d[k];
-      if (Bm) for (int k = 0; k < 7; ++k) Bm[(i * 13 + r) * 7 + k] = s[r].d[13 + k];
-    }
-  }
+  linearize_nd<20>(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, nullptr, threads);
+}
+
+void cpuref_linearize_dt(const AircParams* p, const AircNNBlob* nn, const double* x, const double* u,
+                         double dt, int64_t n, int substeps, uint32_t flags, double* xn, double* A,
+                         double* Bm, double* Dt, int threads) {
+  linearize_nd<21>(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, Dt, threads);
 }
 
 // costs of explicit control sequences: x0[B][13], U[B][H][7] (or shared [H][7]) -> cost[B]

@@ -48,6 +48,8 @@ class CpuRef:
                                             C.c_int, C.c_uint32, vp, vp, C.c_int]
         self.lib.cpuref_linearize.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
                                               C.c_uint32, _f64, _f64, _f64, C.c_int]
+        self.lib.cpuref_linearize_dt.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
+                                                 C.c_uint32, _f64, _f64, _f64, _f64, C.c_int]
 
         _CPp, _SPp = C.POINTER(AircCostParams), C.POINTER(AircSweepParams)
         self.lib.cpuref_rollout_cost.argtypes = [_PP, _NP, _f64, _f64, C.c_double, C.c_int64, C.c_int,
@@ -117,10 +119,15 @@ class CpuRef:
                                 X.ctypes.data if trajectory else None, xf.ctypes.data, self.threads)
         return X if trajectory else xf
 
-    def linearize(self, x, u, dt, substeps=1, normalise=False):
+    def linearize(self, x, u, dt, substeps=1, normalise=False, want_dt=False):
         x, u = np.ascontiguousarray(x, np.float64), np.ascontiguousarray(u, np.float64)
         n = x.shape[0]
         xn, A, Bm = np.empty((n, 13)), np.empty((n, 13, 13)), np.empty((n, 13, 7))
+        if want_dt:
+            Dt = np.empty((n, 13))
+            self.lib.cpuref_linearize_dt(*self._pb(), x, u, float(dt), n, substeps, 1 if normalise else 0,
+                                         xn, A, Bm, Dt, self.threads)
+            return xn, A, Bm, Dt
         self.lib.cpuref_linearize(*self._pb(), x, u, float(dt), n, substeps, 1 if normalise else 0,
                                   xn, A, Bm, self.threads)
         return xn, A, Bm
@@ -140,6 +147,7 @@ class HostEmul:
                                             C.c_uint32, _f32, _f32, _f32]
 
         self.lib.emul_linearize_packed.argtypes = self.lib.emul_linearize.argtypes
+        self.lib.emul_linearize_packed_dt.argtypes = self.lib.emul_linearize.argtypes + [_f32]
         self.lib.emul_sweep_controls.argtypes = [C.POINTER(AircSweepParams), _f32, C.c_int, C.c_int64,
                                                  C.c_int64, _f32]
 
@@ -151,12 +159,17 @@ class HostEmul:
         self.lib.emul_sweep_controls(C.byref(sweep_params), U_nom, H, first, count, U)
         return U
 
-    def linearize_packed(self, x, u, dt, substeps=1, normalise=False):
+    def linearize_packed(self, x, u, dt, substeps=1, normalise=False, want_dt=False):
         """The cooperative kernel's arithmetic (packed two-column tangents), one lane per node."""
         x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
         n = x.shape[0]
         xn = np.empty((n, 13), np.float32)
         A, Bm = np.zeros((n, 13, 13), np.float32), np.zeros((n, 13, 7), np.float32)
+        if want_dt:
+            Dt = np.zeros((n, 13), np.float32)
+            self.lib.emul_linearize_packed_dt(C.byref(self.params), C.byref(self.blob), x, u, float(dt), n,
+                                              substeps, 1 if normalise else 0, xn, A, Bm, Dt)
+            return xn, A, Bm, Dt
         self.lib.emul_linearize_packed(C.byref(self.params), C.byref(self.blob), x, u, float(dt), n,
                                        substeps, 1 if normalise else 0, xn, A, Bm)
         return xn, A, Bm

@@ -100,14 +100,14 @@ void emul_linearize(const AircParams* p, const AircNNBlob* nn, const float* x, c
 
 // The K2 arithmetic: packed (two-column) tangents through rk4_step_lin with the cooperative network
 // policy degenerated to one lane (L = 1, no shuffles).  A[n][13][13], B[n][13][7].
-void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
-                           float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
-                           float* Bm) {
+static void linearize_packed_impl(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                                  float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                                  float* Bm, float* Dt) {
   DevConst P;
   build_devconst(*p, *nn, P);
   const NetCoop<1> net{&P.net, 0};
   for (int64_t i = 0; i < n; ++i) {
-    for (int pair = 0; pair < 7; ++pair) {          // slots (0,1) .. (12,13) as in the kernel
+    for (int pair = 0; pair < (Dt ? 8 : 7); ++pair) {  // slots (0,1) .. (12,13), (14 = dt, 15 idle) as in the kernel
       State s; Ctl c;
       load(x + 13 * i, u + 7 * i, s, c);
       const int s0 = 2 * pair, s1 = 2 * pair + 1;
@@ -116,6 +116,7 @@ void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const floa
       for (int k = 0; k < 3; ++k) { D.p[k] = F2{0.f, 0.f}; D.v[k] = seed(k); D.w[k] = seed(7 + k); }
       for (int k = 0; k < 4; ++k) D.q[k] = seed(3 + k);
       D.dc.da = seed(10); D.dc.de = seed(11); D.dc.dr = seed(12); D.dc.df = seed(13);
+      D.ddt = seed(14);
       state_update_lin<F2>(P, net, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, D);
       if (pair == 0) store(s, xn + 13 * i);
       F2 col[13];
@@ -127,7 +128,8 @@ void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const floa
         for (int hlf = 0; hlf < 2; ++hlf) {
           const int slot = 2 * pair + hlf;
           if (slot < 10) A[(i * 13 + r) * 13 + 3 + slot] = vals[hlf];
-          else Bm[(i * 13 + r) * 7 + bcol[slot - 10]] = vals[hlf];
+          else if (slot < 14) Bm[(i * 13 + r) * 7 + bcol[slot - 10]] = vals[hlf];
+          else if (slot == 14) Dt[i * 13 + r] = vals[hlf];
         }
       }
     }
@@ -136,6 +138,18 @@ void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const floa
       for (int cc = 3; cc < 6; ++cc) Bm[(i * 13 + r) * 7 + cc] = 0.0f;
     }
   }
+}
+
+void emul_linearize_packed(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                           float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                           float* Bm) {
+  linearize_packed_impl(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, nullptr);
+}
+// ... plus the dPhi/d(dt) column, Dt[n][13]
+void emul_linearize_packed_dt(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u,
+                              float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                              float* Bm, float* Dt) {
+  linearize_packed_impl(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, Dt);
 }
 
 // the product's sampler (airc_sampler.cuh) on the host: U[count][H][7]

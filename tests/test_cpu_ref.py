@@ -66,3 +66,16 @@ def test_stall_scaling(built):
     xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01)
     assert np.abs(xn - xo.numpy()).max() < 1e-9 * np.abs(xo.numpy()).max()
     assert np.abs(A - Ao.numpy()).max() < 1e-8 * np.abs(Ao.numpy()).max()
+
+
+def test_linearize_dt_column(pair):
+    ref, orc = pair
+    x, u = make_states(64, seed=15, perturb_norm=1e-3).astype(np.float64), make_controls(64, seed=15).astype(np.float64)
+    xn, A, B, Dt = ref.linearize(x, u, 0.02, 2, True, want_dt=True)
+    xo, Ao, Bo, Do = orc.linearize(t64(x), t64(u), 0.02, 2, True, want_dt=True)
+    assert np.allclose(Dt, Do.numpy(), rtol=1e-9, atol=1e-9)
+    assert np.allclose(A, Ao.numpy(), rtol=1e-9, atol=1e-9) and np.allclose(B, Bo.numpy(), rtol=1e-9, atol=1e-9)
+    # central difference in dt
+    e = 1e-6
+    fd = (ref.state_update(x, u, 0.02 + e, 2, True) - ref.state_update(x, u, 0.02 - e, 2, True)) / (2 * e)
+    assert np.allclose(Dt, fd, rtol=1e-6, atol=1e-6)

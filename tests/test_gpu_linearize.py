@@ -123,3 +123,27 @@ def test_sharded_sweep_single_process(ac):
     assert res.argmin == j and res.owner == 0
     assert torch.equal(res.best_trajectory, full.trajectory[j])
     assert torch.equal(res.best_controls, f32(U[j]))
+
+
+@pytest.mark.parametrize("substeps,normalise,dt", [(1, False, 0.01), (3, True, 0.03)])
+def test_linearize_dt_column(ac, orc, substeps, normalise, dt):
+    """dPhi/d(dt) from the spare tangent slot of K2 (airc_linearize_dt): parity with jacfwd of the
+    float64 oracle, unchanged A/B/x+, both layouts, host path, and a central difference in dt."""
+    n = 4099
+    x, u = make_states(n, seed=45, perturb_norm=1e-3), make_controls(n, seed=45)
+    xn, A, B, Dt = ac.linearize(f32(x), f32(u), dt, substeps=substeps, normalise=normalise, want_dt=True)
+    xo, Ao, Bo, Do = orc.linearize(t64(x), t64(u), dt, substeps, normalise, want_dt=True)
+    assert Dt.shape == (n, 13)
+    assert col_err(Dt.cpu(), Do.numpy()) < PARITY_TOL
+    x3, A3, B3 = ac.linearize(f32(x), f32(u), dt, substeps=substeps, normalise=normalise)
+    assert torch.equal(A, A3) and torch.equal(B, B3) and torch.equal(xn, x3)
+    xs, As, Bs, Ds = ac.linearize(f32(x.T), f32(u.T), dt, substeps=substeps, normalise=normalise,
+                                  layout="soa", want_dt=True)
+    assert Ds.shape == (13, n) and torch.equal(Ds.T, Dt)
+    hx, hA, hB, hD = ac.linearize(x[:257], u[:257], dt, substeps=substeps, normalise=normalise, want_dt=True)
+    assert isinstance(hD, np.ndarray) and np.array_equal(hD, Dt[:257].cpu().numpy())
+    # per-node dt: the column is evaluated at each node's own step size
+    dts = np.linspace(0.5 * dt, 1.5 * dt, n).astype(np.float32)
+    _, _, _, Dn = ac.linearize(f32(x), f32(u), f32(dts), substeps=substeps, normalise=normalise, want_dt=True)
+    _, _, _, Dno = orc.linearize(t64(x), t64(u), t64(dts), substeps, normalise, want_dt=True)
+    assert col_err(Dn.cpu(), Dno.numpy()) < PARITY_TOL

@@ -186,3 +186,35 @@ def test_argmin(ac):
     assert int(i) == 77 and float(m) == -1.5       # lowest index among ties, NaN ignored
     m, i = ac.argmin(torch.tensor([3.0], device=DEV))
     assert int(i) == 0 and float(m) == 3.0
+
+
+def test_diagnostics_side_functions(ac, orc):
+    """v_frd_rel, airspeed, alpha, beta, qbar, coefficients, forces_frd, moments_frd, Euler angles
+    (base.py:147-241,253-278; aircraft.py:255-330) against the float64 oracle, device and host paths."""
+    n = 20011
+    x, u = make_states(n, seed=41, perturb_norm=1e-3), make_controls(n, seed=41)
+    d = ac.diagnostics(f32(x.T), f32(u.T))
+    vb, V, al, be, qb = orc.aero_inputs(t64(x))
+    want = {"v_frd_rel": vb, "airspeed": V, "alpha": al, "beta": be, "qbar": qb,
+            "coefficients": orc.coefficients(t64(x), t64(u)), "forces_frd": orc.forces_frd(t64(x), t64(u)),
+            "moments_frd": orc.moments_frd(t64(x), t64(u))}
+    eul = orc.euler(t64(x))
+    want.update(phi=eul[:, 0], theta=eul[:, 1], psi=eul[:, 2])
+    for k, w in want.items():
+        g = d[k].cpu().numpy()
+        g = g.T if g.ndim == 2 else g[:, None]
+        w = w.numpy() if w.ndim == 2 else w.numpy()[:, None]
+        # angles that wrap (psi over +-180 deg): compare on the circle
+        if k in ("phi", "psi"):
+            diff = np.abs(np.angle(np.exp(1j * (g - w)))).max()
+            assert diff < 2e-6, (k, diff)
+        else:
+            assert col_err(g, w) < PARITY_TOL, (k, col_err(g, w))
+    # reference-style single calls and the host path
+    assert torch.equal(ac.alpha(f32(x.T), f32(u.T)), d["alpha"])
+    assert torch.equal(ac.forces_frd(f32(x.T), f32(u.T)), d["forces_frd"])
+    assert torch.equal(ac.theta(f32(x.T)), d["theta"])
+    one = ac.diagnostics(x[5], u[5])                       # numpy, one column -> host entry point
+    assert one["v_frd_rel"].shape == (3,) and one["coefficients"].shape == (6,)
+    assert abs(float(one["qbar"]) - float(d["qbar"][5])) <= 1e-6 * float(d["qbar"][5])
+    assert np.allclose(one["moments_frd"], d["moments_frd"][:, 5].cpu().numpy(), rtol=1e-5, atol=1e-5)

@@ -74,3 +74,19 @@ def test_linearize_packed_with_stall_scaling(built):
     xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01)
     assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
     assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+
+
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (3, True)])
+def test_linearize_packed_dt_column(pair, substeps, normalise):
+    """dPhi/d(dt) carried in tangent slot 14 of the cooperative kernel's arithmetic, against
+    jacfwd w.r.t. dt of the float64 oracle; A and B are unchanged by the extra slot."""
+    emu, orc = pair
+    x, u = make_states(512, seed=26, perturb_norm=1e-3), make_controls(512, seed=26)
+    xn, A, B, Dt = emu.linearize_packed(x, u, 0.02, substeps, normalise, want_dt=True)
+    xo, Ao, Bo, Do = orc.linearize(t64(x), t64(u), 0.02, substeps, normalise, want_dt=True)
+    assert col_err(Dt, Do.numpy(), atol=1e-3) < PARITY_TOL
+    x2, A2, B2 = emu.linearize_packed(x, u, 0.02, substeps, normalise)
+    assert np.array_equal(A, A2) and np.array_equal(B, B2) and np.array_equal(xn, x2)
+    # d/d(dt) of an RK4 step at dt -> 0 is f(x,u): first-order consistency of the column
+    _, _, _, D0 = orc.linearize(t64(x), t64(u), 1e-9, 1, False, want_dt=True)
+    assert np.allclose(D0.numpy(), orc.state_derivative(t64(x), t64(u)).numpy(), rtol=1e-6, atol=1e-6)
