@@ -55,6 +55,7 @@ class AircSweepParams(C.Structure):
 
 SWEEP_RECORD_HEADER = 4
 NDIAG = 22
+NZ = 21          # z = (x 13, u 7, dt): AIRC_NZ
 DIAG_SLICES = {"v_frd_rel": slice(0, 3), "airspeed": 3, "alpha": 4, "beta": 5, "qbar": 6,
                "coefficients": slice(7, 13), "forces_frd": slice(13, 16), "moments_frd": slice(16, 19),
                "phi": 19, "theta": 20, "psi": 21}
@@ -85,6 +86,8 @@ PROTOTYPES = {
                                  _vp]),
     "airc_linearize_dt": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                     _vp, _vp]),
+    "airc_hessian": (C.c_int, [_vp, _vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp, _vp]),
+    "airc_hessian_host": (C.c_int, [_vp, _vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),
     "airc_sweep_record_floats": (C.c_int64, [_i32]),
     "airc_sweep_workspace_bytes": (C.c_size_t, [_i64, _i32, _i32]),

@@ -26,7 +26,7 @@ from typing import Any, Callable, Dict, Optional, Sequence
 import numpy as np
 
 from . import _cabi
-from ._cabi import (FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX)
+from ._cabi import (FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX, NZ)
 from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH)
 from .params import load_nn_blob, make_cost_params, make_params, make_sweep_params
@@ -442,6 +442,61 @@ class Aircraft:
                    lib, "airc_rollout_host")
             X, xf, cst = (None if a is None else self._like(a, x0) for a in (X, xf, cst))
         return RolloutResult(final=xf, trajectory=X, cost=cst)
+
+    def lagrangian_hessian(self, x, u, lam, dt, *, substeps: Optional[int] = None,
+                           normalise: Optional[bool] = None, layout: str = "aos",
+                           want_grad: bool = True, want_value: bool = False):
+        """H = d2(lam^T Phi)/dz2 with z = (x, u, dt) at every node: the per-node block of the exact
+        Lagrangian Hessian that the reference's IPOPT setup requests from CasADi
+        (config.py:29 hessian_approximation 'exact'; constraints control/base.py:275-286; the dt
+        row/column serves time='progress', control/base.py:276,306-307).
+
+        layout 'aos': x[...,13], u[...,7], lam[...,13] -> H[...,21,21], grad[...,21], value[...]
+        layout 'soa': x[13,N],  u[7,N],  lam[13,N]   -> H[21,21,N],   grad[21,N],   value[N]
+        Returns (H, grad, value) with None for the parts not requested."""
+        if layout not in ("aos", "soa"):
+            raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
+        soa = layout == "soa"
+        on_dev = self._on_device(x, u)
+        if on_dev:
+            xd, ud, ld = (self._dev32(a if _is_torch(a) else torch.as_tensor(a).cuda(self._device), nm)
+                          for a, nm in ((x, "x"), (u, "u"), (lam, "lam")))
+        else:
+            xd, ud, ld = self._host32(x, "x"), self._host32(u, "u"), self._host32(lam, "lam")
+        if soa:
+            if xd.ndim != 2 or xd.shape[0] != NX or ud.ndim != 2 or ud.shape[0] != NU or \
+                    xd.shape[1] != ud.shape[1] or tuple(ld.shape) != tuple(xd.shape):
+                raise RuntimeError(f"soa lagrangian_hessian wants x[13,N], u[7,N], lam[13,N]; got "
+                                   f"{tuple(xd.shape)}, {tuple(ud.shape)}, {tuple(ld.shape)}")
+            n = xd.shape[1]
+            shp_H, shp_g, shp_v = (NZ, NZ, n), (NZ, n), (n,)
+        else:
+            if xd.shape[-1] != NX or ud.shape[-1] != NU or xd.shape[:-1] != ud.shape[:-1] or \
+                    tuple(ld.shape) != tuple(xd.shape):
+                raise RuntimeError(f"aos lagrangian_hessian wants x[...,13], u[...,7], lam[...,13]; got "
+                                   f"{tuple(xd.shape)}, {tuple(ud.shape)}, {tuple(ld.shape)}")
+            lead = tuple(xd.shape[:-1])
+            n = int(np.prod(lead)) if lead else 1
+            shp_H, shp_g, shp_v = lead + (NZ, NZ), lead + (NZ,), lead
+        dts, dtn = self._dt_args(dt, n, on_dev)
+        mk = (lambda s: torch.empty(s, dtype=torch.float32, device=xd.device)) if on_dev else \
+            (lambda s: np.empty(s, np.float32))
+        H = mk(shp_H)
+        g = mk(shp_g) if want_grad else None
+        v = mk(shp_v) if want_value else None
+        lib, h = self._lib, self.handle
+        lay = LAYOUT_SOA if soa else LAYOUT_AOS
+        ns, fl = self._substeps(substeps), self._flags(normalise)
+        if on_dev:
+            _check(lib.airc_hessian(h, xd.data_ptr(), ud.data_ptr(), ld.data_ptr(), dts, self._ptr(dtn), n, ns,
+                                    fl, lay, H.data_ptr(), self._ptr(g), self._ptr(v), self._stream()),
+                   lib, "airc_hessian")
+        else:
+            _check(lib.airc_hessian_host(h, xd.ctypes.data, ud.ctypes.data, ld.ctypes.data, dts, self._ptr(dtn),
+                                         n, ns, fl, lay, H.ctypes.data, self._ptr(g), self._ptr(v)),
+                   lib, "airc_hessian_host")
+            H, g, v = (None if a is None else self._like(a, x) for a in (H, g, v))
+        return H, g, v
 
     def linearize(self, x, u, dt, *, substeps: Optional[int] = None,
                   normalise: Optional[bool] = None, layout: str = "aos",

@@ -10,6 +10,7 @@
 #include "airc_fuse.hpp"
 #include "airc_kernels.cuh"
 #include "airc_kernels2.cuh"
+#include "airc_hess.cuh"
 #include "airc_peak.cuh"
 #include "airc_sweep.cuh"
 #include "airc_sweep2.cuh"
@@ -257,6 +258,34 @@ int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float
   if (dPhi_ddt) return fail(AIRC_EINVAL, "airc_linearize_dt: not available in the AIRC_LIN_V1 build%s", "");
 #endif
   return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt, stream);
+}
+
+int airc_hessian(const AircHandle* h, const float* x, const float* u, const float* lam, float dt,
+                 const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                 float* H, float* grad, float* value, void* stream) {
+  if (!h || !x || !u || !lam || !H || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
+      (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
+    return fail(AIRC_EINVAL, "airc_hessian: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  cudaStream_t st = (cudaStream_t)stream;
+  // rows/columns of p and thrust are structurally zero; the kernel writes the 15x15 active block
+  CUDA_TRY(cudaMemsetAsync(H, 0, (size_t)n * AIRC_NZ * AIRC_NZ * sizeof(float), st));
+  HessArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x = view(x, n, 13, layout);
+  a.u = view(u, n, 7, layout);
+  a.lam = view(lam, n, 13, layout);
+  a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
+  a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+  a.H = H; a.grad = grad; a.value = value;
+  const int bs = 128;
+  const long long threads = n * HESS_LANES;
+  const unsigned grid = (unsigned)((threads + bs - 1) / bs);
+  if (layout == AIRC_LAYOUT_SOA) hessian_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
+  else hessian_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+  return check_launch();
 }
 
 int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
@@ -637,6 +666,38 @@ int airc_linearize_dt_host(AircHandle* h, const float* x, const float* u, float 
                            const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                            int layout, float* x_next, float* A, float* Bm, float* dPhi_ddt) {
   return linearize_host_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt);
+}
+
+int airc_hessian_host(AircHandle* h, const float* x, const float* u, const float* lam, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                      float* H, float* grad, float* value) {
+  if (!h || !x || !u || !lam || !H || n < 0) return fail(AIRC_EINVAL, "airc_hessian_host: bad argument%s", "");
+  if (n == 0) return AIRC_OK;
+  DeviceGuard g(h->device);
+  if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+  const size_t bx = al(13 * n), bu = al(7 * n), bH = al((size_t)AIRC_NZ * AIRC_NZ * n);
+  const size_t bg = grad ? al((size_t)AIRC_NZ * n) : 0, bv = value ? al(n) : 0, bd = dt_per_node ? al(n) : 0;
+  int rc = ensure_scratch(h, 2 * bx + bu + bH + bg + bv + bd);
+  if (rc) return rc;
+  char* base = (char*)h->scratch;
+  float* dx = (float*)base;
+  float* dl = (float*)(base + bx);
+  float* du = (float*)(base + 2 * bx);
+  float* dH = (float*)(base + 2 * bx + bu);
+  float* dg = grad ? (float*)(base + 2 * bx + bu + bH) : nullptr;
+  float* dv = value ? (float*)(base + 2 * bx + bu + bH + bg) : nullptr;
+  float* ddt = dt_per_node ? (float*)(base + 2 * bx + bu + bH + bg + bv) : nullptr;
+  if (ddt) CUDA_TRY(cudaMemcpyAsync(ddt, dt_per_node, n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(dx, x, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(dl, lam, 13 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  CUDA_TRY(cudaMemcpyAsync(du, u, 7 * n * sizeof(float), cudaMemcpyHostToDevice, h->hstream));
+  rc = airc_hessian(h, dx, du, dl, dt, ddt, n, substeps, flags, layout, dH, dg, dv, h->hstream);
+  if (rc) return rc;
+  CUDA_TRY(cudaMemcpyAsync(H, dH, (size_t)AIRC_NZ * AIRC_NZ * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (grad) CUDA_TRY(cudaMemcpyAsync(grad, dg, (size_t)AIRC_NZ * n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  if (value) CUDA_TRY(cudaMemcpyAsync(value, dv, n * sizeof(float), cudaMemcpyDeviceToHost, h->hstream));
+  CUDA_TRY(cudaStreamSynchronize(h->hstream));
+  return AIRC_OK;
 }
 
 int airc_sweep_host(AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,

@@ -1,0 +1,166 @@
+// airc_hess.cuh -- K3: Hessian of the multiplier-weighted step, H = d2 (lambda^T Phi) / dz2 with
+// z = (x[13], u[7], dt), and its gradient, at n shooting nodes.
+//
+// Replaces CasADi's second-order AD behind IPOPT's exact nlp_hess_l
+// (/root/reference/src/aircraft/config.py:29; constraints control/base.py:275-286; the dt row and
+// column belong to time='progress', control/base.py:276,306-307).
+//
+// 15 directions are active: v(3) q(4) w(3) aileron elevator rudder flaps dt.  p never enters f and
+// thrust is inert (aircraft.py:320), so their rows/columns of H are exactly zero and are left to the
+// caller's memset.  The 120 entries (i <= j) of the symmetric 15x15 block are computed by 64 threads
+// per node: thread t owns one outer direction i and a PAIR of inner directions (j, j+1), packed
+// into the two lanes of FFMA2 (airc_jet.cuh).
+#pragma once
+#include "airc_jet.cuh"
+#include "airc_step.cuh"
+#if defined(__CUDACC__)
+#include "airc_kernels.cuh"
+#endif
+
+namespace airc {
+
+constexpr int NHACT = 15;       // active directions
+constexpr int NZ = 21;          // z = (x 13, u 7, dt)
+constexpr int HESS_LANES = 64;  // sum_{i<15} ceil((15-i)/2)
+
+// thread t of a node -> outer direction i, inner pair (j0, j1); j1 == NHACT means "no second entry"
+AIRC_HD void hess_task(int t, int& i, int& j0, int& j1) {
+  int acc = 0;
+  for (i = 0; i < NHACT; ++i) {
+    const int cnt = (NHACT - i + 1) >> 1;
+    if (t < acc + cnt) {
+      j0 = i + 2 * (t - acc);
+      j1 = j0 + 1;
+      return;
+    }
+    acc += cnt;
+  }
+  i = j0 = j1 = NHACT;
+}
+
+// active direction -> index in z
+AIRC_HD int hess_zindex(int d) {
+  return d < 13 ? 3 + d : (d == 13 ? 19 : 20);
+}
+
+struct HessSeed {
+  int i, j0, j1;
+  AIRC_HD Jet operator()(float val, int slot) const {
+    return Jet{val, slot == i ? 1.0f : 0.0f, F2{slot == j0 ? 1.0f : 0.0f, slot == j1 ? 1.0f : 0.0f}, F2{0.0f, 0.0f}};
+  }
+};
+
+// lambda^T Phi(x,u,dt) on jets.  lam[13] in state order.  Returns the jet of the scalar.
+AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c0, float dt, int substeps,
+                                bool normalise, const float lam[13], const HessSeed& seed) {
+  Jet v[3], q[4], w[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { v[i] = seed(x0.v[i], i); w[i] = seed(x0.w[i], 7 + i); }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) q[i] = seed(x0.q[i], 3 + i);
+  CtlJ c{seed(c0.da, 10), seed(c0.de, 11), seed(c0.dr, 12), seed(c0.df, 13)};
+  const float is = 1.0f / (float)substeps;
+  const Jet h = is * seed(dt, 14);
+  const Jet hh = 0.5f * h, h6 = (1.0f / 6.0f) * h;
+  // lambda_p . p+ : p+ = p + sum over substeps of h/6 (v1 + 2 v2 + 2 v3 + v4), never fed back into f
+  Jet Lp = jconst((lam[0] * x0.p[0] + lam[1] * x0.p[1]) + lam[2] * x0.p[2]);
+  for (int sub = 0; sub < substeps; ++sub) {
+    Jet sv[3], sq[4], sw[3], av[3], aq[4], aw[3];
+    Jet ap = jconst(0.0f);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { sv[i] = v[i]; sw[i] = w[i]; av[i] = jconst(0.0f); aw[i] = jconst(0.0f); }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { sq[i] = q[i]; aq[i] = jconst(0.0f); }
+#pragma unroll 1
+    for (int stage = 0; stage < 4; ++stage) {
+      const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
+      Jet kv[3], kq[4], kw[3];
+      f_jet(P, sv, sq, sw, c, kv, kq, kw);
+      ap = jfma(wgt, jfma(lam[2], sv[2], jfma(lam[1], sv[1], lam[0] * sv[0])), ap);
+      const Jet cn = (stage == 2) ? h : hh;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        av[i] = jfma(wgt, kv[i], av[i]);
+        aw[i] = jfma(wgt, kw[i], aw[i]);
+        sv[i] = jmad(cn, kv[i], v[i]);
+        sw[i] = jmad(cn, kw[i], w[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        aq[i] = jfma(wgt, kq[i], aq[i]);
+        sq[i] = jmad(cn, kq[i], q[i]);
+      }
+    }
+    Lp = jmad(h6, ap, Lp);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { v[i] = jmad(h6, av[i], v[i]); w[i] = jmad(h6, aw[i], w[i]); }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] = jmad(h6, aq[i], q[i]);
+  }
+  if (normalise) {   // q <- q/|q| (base.py:443-444, 473-474)
+    const Jet rn = jrsqrt((q[0] * q[0] + q[1] * q[1]) + (q[2] * q[2] + q[3] * q[3]));
+#pragma unroll
+    for (int i = 0; i < 4; ++i) q[i] = q[i] * rn;
+  }
+  Jet L = Lp;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { L = jfma(lam[3 + i], v[i], L); L = jfma(lam[10 + i], w[i], L); }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) L = jfma(lam[6 + i], q[i], L);
+  return L;
+}
+
+#if defined(__CUDACC__)
+struct HessArgs {
+  VecView x, u, lam;         // [13|7|13] per node
+  const float* dt_per_node;  // optional
+  float dt;
+  long long n;
+  int substeps, normalise;
+  float* H;                  // SoA [441][n] / AoS [n][21][21]; zero-filled by the caller of the kernel
+  float* grad;               // optional, SoA [21][n] / AoS [n][21]
+  float* value;              // optional [n]: lambda^T Phi
+};
+
+template <bool SOA>
+__global__ void __launch_bounds__(128)
+hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long node = gt / HESS_LANES;
+  if (node >= a.n) return;
+  const int t = (int)(gt % HESS_LANES);
+  HessSeed seed;
+  hess_task(t, seed.i, seed.j0, seed.j1);
+  State s;
+  load_state(a.x, node, s);
+  const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
+  float lam[13];
+#pragma unroll
+  for (int r = 0; r < 13; ++r) lam[r] = __ldg(a.lam.base + node * a.lam.sb + r * a.lam.sc);
+  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
+  const Jet L = lagrangian_step_jet(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed);
+  const long long es = SOA ? a.n : 1;
+  float* Hn = a.H + (SOA ? node : node * (NZ * NZ));
+  const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);
+  Hn[(zi * NZ + z0) * es] = L.og.lo;
+  Hn[(z0 * NZ + zi) * es] = L.og.lo;
+  if (seed.j1 < NHACT) {
+    const int z1 = hess_zindex(seed.j1);
+    Hn[(zi * NZ + z1) * es] = L.og.hi;
+    Hn[(z1 * NZ + zi) * es] = L.og.hi;
+  }
+  if (seed.j0 == seed.i) {   // the first task of every outer direction also owns the gradient entry
+    if (a.grad) {
+      float* g = a.grad + (SOA ? node : node * NZ);
+      g[zi * es] = L.o;
+      if (seed.i == 0) {     // inactive rows: d/dp = lambda_p (dPhi/dp = [I;0]), d/dthrust = 0
+#pragma unroll
+        for (int r = 0; r < 3; ++r) { g[r * es] = lam[r]; g[(16 + r) * es] = 0.0f; }
+      }
+    }
+    if (a.value && seed.i == 0) a.value[node] = L.v;
+  }
+}
+#endif
+
+}  // namespace airc

@@ -166,6 +166,20 @@ int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float
                       const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
                       float* x_next, float* A, float* Bm, float* dPhi_ddt, void* stream);
 
+/* Second-order products for the solver: H = d2(lambda^T Phi)/dz2 with z = (x[13], u[7], dt), the
+ * per-node block of the Lagrangian Hessian that IPOPT obtains from CasADi with
+ * hessian_approximation 'exact' (src/aircraft/config.py:29; constraints control/base.py:275-286; the
+ * dt row/column serves time='progress', control/base.py:276,306-307).  Second-order forward mode
+ * on 64 threads per node (15 active directions; rows/columns of p and thrust are exactly zero).
+ *   lam   multipliers of the 13 rows of Phi, laid out like x
+ *   H     SOA [21*21][n] / AOS [n][21][21], full symmetric matrix (required)
+ *   grad  optional d(lambda^T Phi)/dz, SOA [21][n] / AOS [n][21]   (= [A B dPhi/ddt]^T lambda)
+ *   value optional lambda^T Phi, [n]                                                          */
+#define AIRC_NZ 21
+int airc_hessian(const AircHandle* h, const float* x, const float* u, const float* lam, float dt,
+                 const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                 float* H, float* grad, float* value, void* stream);
+
 /* (min, argmin) of cost[B] by warp-shuffle + 64-bit atomicMin; ties go to the lower index.
  * out_min: 1 float, out_idx: 1 int64 (device). */
 int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_min,
@@ -243,6 +257,9 @@ int airc_rollout_host(AircHandle* h, const float* x0, const float* U, float dt, 
 int airc_linearize_host(AircHandle* h, const float* x, const float* u, float dt,
                         const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                         int layout, float* x_next, float* A, float* Bm);
+int airc_hessian_host(AircHandle* h, const float* x, const float* u, const float* lam, float dt,
+                      const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                      float* H, float* grad, float* value);
 int airc_linearize_dt_host(AircHandle* h, const float* x, const float* u, float dt,
                            const float* dt_per_node, int64_t n, int substeps, uint32_t flags,
                            int layout, float* x_next, float* A, float* Bm, float* dPhi_ddt);

@@ -300,6 +300,23 @@ class AircraftOracle:
         A, Bm = jac(x, u, dtt)
         return phi(x, u, dtt), A, Bm
 
+    # ---- H = d2(lam^T Phi)/dz2, z = (x, u, dt): the per-node block of IPOPT's exact Lagrangian Hessian
+    #      (config.py:29 hessian_approximation 'exact'; constraints control/base.py:275-286)
+    def lagrangian_hessian(self, x, u, lam, dt, substeps=None, normalise=None):
+        x = torch.as_tensor(x, dtype=F64).reshape(-1, 13)
+        u = torch.as_tensor(u, dtype=F64).reshape(-1, 7)
+        lam = torch.as_tensor(lam, dtype=F64).reshape(-1, 13)
+        dtt = torch.as_tensor(dt, dtype=F64).expand(x.shape[0]) if torch.as_tensor(dt).ndim == 0 \
+            else torch.as_tensor(dt, dtype=F64).reshape(-1)
+        z = torch.cat([x, u, dtt[:, None]], dim=1)
+
+        def L(zi, li):
+            return (li * self.state_update(zi[:13], zi[13:20], zi[20], substeps, normalise)).sum()
+
+        H = torch.func.vmap(torch.func.jacfwd(torch.func.jacfwd(L)))(z, lam)
+        g = torch.func.vmap(torch.func.jacfwd(L))(z, lam)
+        return H, g, torch.func.vmap(L)(z, lam)
+
     # ---- primary MPC cost (main/control/control.py:35-70) on a rollout X[B,H+1,13], U[B,H,7]
     def cost(self, X, U, goal=(150.0, 0.0), vel_param=1.0):
         X = torch.as_tensor(X, dtype=F64)

@@ -11,6 +11,7 @@
 #include "../aircraft_b200/csrc/airc_step.cuh"
 #include "../aircraft_b200/csrc/airc_coop.cuh"
 #include "../aircraft_b200/csrc/airc_sampler.cuh"
+#include "../aircraft_b200/csrc/airc_hess.cuh"
 
 using namespace airc;
 
@@ -150,6 +151,35 @@ void emul_linearize_packed_dt(const AircParams* p, const AircNNBlob* nn, const f
                               float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
                               float* Bm, float* Dt) {
   linearize_packed_impl(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, Dt);
+}
+
+// K3 arithmetic (airc_hess.cuh): the 64 (outer, inner-pair) tasks of a node, one after the other.
+// H[n][21][21] (zero-filled here), grad[n][21], value[n]
+void emul_hessian(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,
+                  float dt, int64_t n, int substeps, uint32_t flags, float* H, float* grad, float* value) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  memset(H, 0, sizeof(float) * NZ * NZ * n);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* Hn = H + i * NZ * NZ;
+    float* g = grad + i * NZ;
+    for (int r = 0; r < 3; ++r) { g[r] = lam[13 * i + r]; g[16 + r] = 0.f; }
+    for (int t = 0; t < HESS_LANES; ++t) {
+      HessSeed seed;
+      hess_task(t, seed.i, seed.j0, seed.j1);
+      const Jet L = lagrangian_step_jet(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, lam + 13 * i, seed);
+      const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);
+      Hn[zi * NZ + z0] = Hn[z0 * NZ + zi] = L.og.lo;
+      if (seed.j1 < NHACT) {
+        const int z1 = hess_zindex(seed.j1);
+        Hn[zi * NZ + z1] = Hn[z1 * NZ + zi] = L.og.hi;
+      }
+      if (seed.j0 == seed.i) g[zi] = L.o;
+      if (t == 0) value[i] = L.v;
+    }
+  }
 }
 
 // the product's sampler (airc_sampler.cuh) on the host: U[count][H][7]

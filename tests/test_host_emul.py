@@ -90,3 +90,37 @@ def test_linearize_packed_dt_column(pair, substeps, normalise):
     # d/d(dt) of an RK4 step at dt -> 0 is f(x,u): first-order consistency of the column
     _, _, _, D0 = orc.linearize(t64(x), t64(u), 1e-9, 1, False, want_dt=True)
     assert np.allclose(D0.numpy(), orc.state_derivative(t64(x), t64(u)).numpy(), rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (2, True)])
+def test_lagrangian_hessian_jets(pair, substeps, normalise):
+    """K3 arithmetic (airc_jet.cuh / airc_hess.cuh: second-order forward mode, 64 (outer, inner-pair)
+    tasks per node) against jacfwd(jacfwd(lam^T Phi)) of the float64 oracle over z = (x, u, dt)."""
+    emu, orc = pair
+    n = 96
+    x, u = make_states(n, seed=27, perturb_norm=1e-3), make_controls(n, seed=27)
+    lam = np.random.default_rng(27).normal(size=(n, 13)).astype(np.float32)
+    H, g, v = emu.hessian(x, u, lam, 0.02, substeps, normalise)
+    Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.02, substeps, normalise))
+    assert col_err(H, Ho, atol=1e-3) < PARITY_TOL        # every entry against its own scale over the batch
+    assert col_err(g, go) < PARITY_TOL
+    assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
+    assert np.array_equal(H, H.transpose(0, 2, 1))
+    inert = [0, 1, 2, 16, 17, 18]                        # p never enters f; thrust is inert (aircraft.py:320)
+    assert not H[:, inert, :].any() and not Ho[:, inert, :].any()
+    # the gradient is [A B dPhi/ddt]^T lam
+    xo, A, B, Dt = orc.linearize(t64(x), t64(u), 0.02, substeps, normalise, want_dt=True)
+    J = np.concatenate([A.numpy(), B.numpy(), Dt.numpy()[:, :, None]], axis=2)
+    assert np.allclose(go, np.einsum("nr,nrz->nz", lam.astype(np.float64), J), rtol=1e-9, atol=1e-9)
+
+
+def test_lagrangian_hessian_jets_stall_scaling(built):
+    p, blob = params_for(stall_scaling=True)
+    emu, orc = HostEmul(p, blob), oracle_for(stall_scaling=True)
+    n = 64
+    x, u = make_states(n, seed=28), make_controls(n, seed=28)
+    x[:32, 3:6] *= np.array([0.6, 1.0, 2.0])             # large alpha: the scaling is active
+    lam = np.random.default_rng(28).normal(size=(n, 13)).astype(np.float32)
+    H, g, v = emu.hessian(x, u, lam, 0.01)
+    Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.01))
+    assert col_err(H, Ho, atol=1e-3) < PARITY_TOL and col_err(g, go) < PARITY_TOL
