@@ -86,6 +86,7 @@ PROTOTYPES = {
                                  _vp]),
     "airc_linearize_dt": (C.c_int, [_vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp,
                                     _vp, _vp]),
+    "airc_defects": (C.c_int, [_vp, _vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp, _vp, _vp]),
     "airc_hessian": (C.c_int, [_vp, _vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp, _vp]),
     "airc_hessian_host": (C.c_int, [_vp, _vp, _vp, _vp, _f, _vp, _i64, _i32, _u32, _i32, _vp, _vp, _vp]),
     "airc_argmin": (C.c_int, [_vp, _vp, _i64, _vp, _vp, _vp]),

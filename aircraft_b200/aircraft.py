@@ -443,6 +443,57 @@ class Aircraft:
             X, xf, cst = (None if a is None else self._like(a, x0) for a in (X, xf, cst))
         return RolloutResult(final=xf, trajectory=X, cost=cst)
 
+    def defects(self, X, U, dt, *, substeps: Optional[int] = None, normalise: Optional[bool] = None,
+                want_dt: bool = False):
+        """Multiple-shooting defects r_k = x_{k+1} - Phi(x_k, u_k, dt_k) with their Jacobian blocks for
+        any number of windows, one launch of the Jacobian kernel (control/base.py:275-279; the warm
+        start / re-linearisation step of MHTT, control/moving_horizon.py:203-246).
+
+        X[..., N+1, 13], U[..., N, 7] (U may carry N+1 rows like the reference's guess array; the last
+        is ignored), dt scalar or [..., N] -> r[..., N, 13], A[..., N, 13, 13], B[..., N, 13, 7]
+        (+ dPhi/d(dt) [..., N, 13] with want_dt).  The constraint Jacobian of the reference's NLP has the
+        blocks d r_k / d(x_k, u_k, x_{k+1}, dt_k) = (-A_k, -B_k, I, -dPhi/d(dt)_k)."""
+        host = not self._on_device(X, U)
+        dev = f"cuda:{self._device}"
+        Xd = torch.as_tensor(np.asarray(X) if not _is_torch(X) else X).to(device=dev, dtype=torch.float32)
+        Ud = torch.as_tensor(np.asarray(U) if not _is_torch(U) else U).to(device=dev, dtype=torch.float32)
+        if Xd.ndim < 2 or Xd.shape[-1] != NX or Ud.ndim != Xd.ndim or Ud.shape[-1] != NU or \
+                Ud.shape[:-2] != Xd.shape[:-2] or Ud.shape[-2] not in (Xd.shape[-2] - 1, Xd.shape[-2]) or \
+                Xd.shape[-2] < 2:
+            raise RuntimeError(f"defects wants X[...,N+1,13], U[...,N,7]; got {tuple(Xd.shape)}, {tuple(Ud.shape)}")
+        N = Xd.shape[-2] - 1
+        lead = tuple(Xd.shape[:-2]) + (N,)
+        n = int(np.prod(lead))
+        x = Xd[..., :-1, :].reshape(n, NX).contiguous()
+        xt = Xd[..., 1:, :].reshape(n, NX).contiguous()
+        u = Ud[..., :N, :].reshape(n, NU).contiguous()
+        if _is_torch(dt) or np.ndim(dt) > 0:
+            dtt = torch.as_tensor(np.asarray(dt) if not _is_torch(dt) else dt)
+            dtt = dtt.to(device=dev, dtype=torch.float32).expand(lead).reshape(n) if dtt.numel() > 1 else float(dtt)
+        else:
+            dtt = float(dt)
+        dts, dtn = self._dt_args(dtt, n, True)
+        mk = lambda *shp: torch.empty(lead + shp, dtype=torch.float32, device=dev)  # noqa: E731
+        r, A, Bm = mk(NX), mk(NX, NX), mk(NX, NU)
+        Dt = mk(NX) if want_dt else None
+        lib = self._lib
+        _check(lib.airc_defects(self.handle, x.data_ptr(), u.data_ptr(), xt.data_ptr(), dts, self._ptr(dtn), n,
+                                self._substeps(substeps), self._flags(normalise), LAYOUT_AOS, r.data_ptr(),
+                                A.data_ptr(), Bm.data_ptr(), self._ptr(Dt), self._stream()),
+               lib, "airc_defects")
+        out = (r, A, Bm, Dt) if want_dt else (r, A, Bm)
+        if host:
+            out = tuple(self._like(o.cpu().numpy(), X) for o in out)
+        return out
+
+    def defects_from_guess(self, guess, dt, **kw):
+        """defects() on the reference's column-per-node guess array [13+7(+extra rows), N+1]
+        (main/control/control.py:72-93, MHTT.set_initial_from_array moving_horizon.py:108-114)."""
+        g = guess if _is_torch(guess) else np.asarray(guess)
+        if g.ndim != 2 or g.shape[0] < NX + NU:
+            raise RuntimeError(f"guess must be [>=20, N+1], got {tuple(g.shape)}")
+        return self.defects(g[:NX].T, g[NX:NX + NU].T, dt, **kw)
+
     def lagrangian_hessian(self, x, u, lam, dt, *, substeps: Optional[int] = None,
                            normalise: Optional[bool] = None, layout: str = "aos",
                            want_grad: bool = True, want_value: bool = False):

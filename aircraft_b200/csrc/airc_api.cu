@@ -215,7 +215,8 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
 
 static int linearize_impl(const AircHandle* h, const float* x, const float* u, float dt,
                           const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
-                          float* x_next, float* A, float* Bm, float* Dt, void* stream) {
+                          float* x_next, float* A, float* Bm, float* Dt, void* stream,
+                          const float* x_target = nullptr, float* defect = nullptr) {
   if (!h || !x || !u || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_linearize: bad argument%s", "");
@@ -228,6 +229,7 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
   a.u = view(u, n, 7, layout);
   a.xn = viewW(x_next, n, 13, layout);
   a.A = A; a.Bm = Bm; a.Dt = Dt;
+  if (defect) { a.xt = view(x_target, n, 13, layout); a.r = viewW(defect, n, 13, layout); }
   if (layout == AIRC_LAYOUT_SOA) { a.A_sn = 1; a.A_se = n; a.B_sn = 1; a.B_se = n; }
   else { a.A_sn = 169; a.A_se = 1; a.B_sn = 91; a.B_se = 1; }
   a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
@@ -258,6 +260,17 @@ int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float
   if (dPhi_ddt) return fail(AIRC_EINVAL, "airc_linearize_dt: not available in the AIRC_LIN_V1 build%s", "");
 #endif
   return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt, stream);
+}
+
+int airc_defects(const AircHandle* h, const float* x, const float* u, const float* x_target, float dt,
+                 const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                 float* defect, float* A, float* Bm, float* dPhi_ddt, void* stream) {
+  if (!x_target || !defect) return fail(AIRC_EINVAL, "airc_defects: bad argument%s", "");
+#ifdef AIRC_LIN_V1
+  return fail(AIRC_EINVAL, "airc_defects: not available in the AIRC_LIN_V1 build%s", "");
+#endif
+  return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, nullptr, A, Bm, dPhi_ddt, stream,
+                        x_target, defect);
 }
 
 int airc_hessian(const AircHandle* h, const float* x, const float* u, const float* lam, float dt,

@@ -254,6 +254,8 @@ struct LinArgs {
   float* Bm;                 // optional; element (node, r, c) at Bm[node*B_sn + (r*7+c)*B_se]
   long long B_sn, B_se;
   float* Dt;                 // optional dPhi/d(dt): SoA [13][n] / AoS [n][13]
+  VecView xt;                // optional: the next node's state guess ...
+  VecViewW r;                // ... and the multiple-shooting defect r = xt - Phi(x,u,dt) (control/base.py:275-279)
   const float* dt_per_node;
   float dt;
   long long n;
@@ -407,6 +409,15 @@ linearize_coop_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
     }
   } else {
     if (a.xn.base) store_state(a.xn, node, s);
+    if (a.r.base) {
+      State t;
+      load_state(a.xt, node, t);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { t.p[i] -= s.p[i]; t.v[i] -= s.v[i]; t.w[i] -= s.w[i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) t.q[i] -= s.q[i];
+      store_state(a.r, node, t);
+    }
     if (a.Dt) {
       float* o = a.Dt + (SOA ? node : node * 13);
 #pragma unroll

@@ -166,6 +166,18 @@ int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float
                       const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
                       float* x_next, float* A, float* Bm, float* dPhi_ddt, void* stream);
 
+/* Multiple-shooting defects with their Jacobian blocks, one node per (window, step) pair:
+ *   defect = x_target - Phi(x, u, dt)          (control/base.py:275-279: next.state - dynamics(...) == 0)
+ * together with A = dPhi/dx, Bm = dPhi/du and (optionally) dPhi/d(dt) from the same launch of the
+ * Jacobian kernel.  The constraint Jacobian of the reference's NLP is block-bidiagonal with blocks
+ * d(defect_k)/d(x_k, u_k, x_{k+1}, dt_k) = (-A_k, -Bm_k, I, -dPhi_ddt_k); these are its blocks, in the form
+ * a Riccati / condensing sweep consumes (MHTT.initialise / update_parameters,
+ * control/moving_horizon.py:203-246).  Layouts as airc_linearize; x_target and defect like x.
+ * A, Bm, dPhi_ddt may each be NULL.                                                                 */
+int airc_defects(const AircHandle* h, const float* x, const float* u, const float* x_target, float dt,
+                 const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
+                 float* defect, float* A, float* Bm, float* dPhi_ddt, void* stream);
+
 /* Second-order products for the solver: H = d2(lambda^T Phi)/dz2 with z = (x[13], u[7], dt), the
  * per-node block of the Lagrangian Hessian that IPOPT obtains from CasADi with
  * hessian_approximation 'exact' (src/aircraft/config.py:29; constraints control/base.py:275-286; the

@@ -147,3 +147,31 @@ def test_linearize_dt_column(ac, orc, substeps, normalise, dt):
     _, _, _, Dn = ac.linearize(f32(x), f32(u), f32(dts), substeps=substeps, normalise=normalise, want_dt=True)
     _, _, _, Dno = orc.linearize(t64(x), t64(u), t64(dts), substeps, normalise, want_dt=True)
     assert col_err(Dn.cpu(), Dno.numpy()) < PARITY_TOL
+
+
+def test_multiple_shooting_defects(ac, orc):
+    """r_k = x_{k+1} - Phi(x_k,u_k,dt) with (A,B,dPhi/ddt) blocks for many windows in one launch
+    (airc_defects); a rollout's own trajectory has zero defect."""
+    W, N = 7, 40
+    x0 = make_states(W, seed=61)
+    U = make_control_sequences(W, N, seed=61)
+    X = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True).trajectory   # [W,N+1,13]
+    r, A, B = ac.defects(X, f32(U), 0.01, normalise=True)
+    assert r.shape == (W, N, 13) and A.shape == (W, N, 13, 13) and B.shape == (W, N, 13, 7)
+    assert float(r.abs().max()) < 2e-5 * float(X.abs().max())     # two kernels, last-ulp differences only
+    # perturbed guess: parity with the oracle on every block
+    g = torch.Generator(device="cpu").manual_seed(5)
+    Xp = X.cpu() + 1e-2 * torch.randn(X.shape, generator=g)
+    r, A, B, Dt = ac.defects(f32(Xp), f32(U), 0.01, normalise=True, want_dt=True)
+    xs, us = Xp[:, :-1].reshape(-1, 13).numpy(), U.reshape(-1, 7)
+    xo, Ao, Bo, Do = orc.linearize(t64(xs), t64(us), 0.01, 1, True, want_dt=True)
+    want_r = Xp[:, 1:].reshape(-1, 13).double().numpy() - xo.numpy()
+    assert col_err(r.reshape(-1, 13).cpu(), want_r, atol=1.0) < PARITY_TOL    # defect scale ~ state scale
+    assert col_err(A.reshape(-1, 13, 13).cpu(), Ao.numpy()) < PARITY_TOL
+    assert col_err(B.reshape(-1, 13, 7).cpu(), Bo.numpy()) < PARITY_TOL
+    assert col_err(Dt.reshape(-1, 13).cpu(), Do.numpy()) < PARITY_TOL
+    # the reference's guess layout [13+7, N+1] and host arrays
+    guess = np.concatenate([Xp[0].numpy().T, np.concatenate([U[0], U[0][-1:]], 0).T], axis=0)
+    rg, Ag, Bg = ac.defects_from_guess(guess, 0.01, normalise=True)
+    assert isinstance(rg, np.ndarray) and rg.shape == (N, 13)
+    assert np.array_equal(rg.astype(np.float32), r[0].cpu().numpy()) and np.array_equal(Ag.astype(np.float32), A[0].cpu().numpy())
