@@ -572,6 +572,16 @@ def side_measurements(torch, ac, dev, rank, args):
     out["c5_shard"] = {"workload": "BASELINE config 5 shard: 1024 windows x 50 nodes per GPU, A[.,13,13], B[.,13,7] (AoS)",
                        "value": n5 / (ms * 1e-3), "unit": "jacobian-evals/s", "ms_per_launch": ms,
                        "l2": "flushed between launches"}
+    # row f.1: exact Lagrangian-Hessian blocks at the reference's horizon (298 nodes, todo.md tables) and in bulk
+    for name, nh in (("hessian_298", 298), ("hessian_bulk", 262_144)):
+        x = torch.tensor(make_states(nh, seed=600 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev).contiguous()
+        u = torch.tensor(make_controls(nh, seed=600 + rank).T, dtype=torch.float32, device=dev).contiguous()
+        lam = torch.randn(13, nh, device=dev, generator=torch.Generator(device=dev).manual_seed(600 + rank))
+        ms = time_launches(torch, lambda: ac.lagrangian_hessian(x, u, lam, DT, layout="soa", normalise=True), K, 3, flush)
+        out[name] = {"workload": f"d2(lambda^T Phi)/d(x,u,dt)^2 [21x21] + gradient at {nh} shooting nodes (SoA)",
+                     "value": nh / (ms * 1e-3), "unit": "hessian-evals/s", "ms_per_launch": ms,
+                     "l2": "flushed between launches",
+                     "reference_context": "nlp_hess_l 56-560 ms per IPOPT iteration at 298 nodes (reference todo.md tables, CPU)"}
     return out
 
 
