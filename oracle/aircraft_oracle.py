@@ -21,11 +21,19 @@ semantics, verified numerically against todo.md -- see tests/test_oracle_golden.
     ``inverse() = conj / ||q||^2``, ``normalize() = q / ||q||``.
   * CasADi 3.6.7 ``atan2, asin, sqrt, sign, cross, inv`` and forward AD (``sign'`` = 0).
 
-Parity status: the quaternion/force conventions are pinned by the three todo.md
-known-answer vectors; the NN block is pinned by importing the reference's own
-``ScaledModel`` (fixtures in tests/golden/); ``state_update`` *with the NN model* is
-pinned by no reference test or artefact ("parity unpinned" for that composition --
-it is pinned only by code reading).
+Parity status: PINNED, in three pieces that together cover the path.
+  1. The quaternion/force conventions by the three todo.md known-answer vectors (DefaultModel).
+  2. The NN block by importing the reference's own ``ScaledModel`` (fixtures in tests/golden/).
+  3. The composition f -> RK4 -> substeps fold (v_frd_rel, alpha/beta/qbar, forces, moments with the com
+     offset, shifted inertia, forces_ned, v_dot, q_dot, omega_dot, state_step, state_update) by a
+     trajectory the reference itself produced and stored: data/trajectories/simulation.h5
+     (main/dynamics/dynamics.py, poly model, 10 substeps, dt 0.1), reproduced to < 1e-12 over all 39
+     steps with ``coeff_model='poly'`` (PolynomialModel restated below from the reference's pickle;
+     tests/test_oracle_golden.py::test_state_update_reproduces_reference_stored_trajectory).
+What no reference artefact exercises is the *combination* of piece 2 inside piece 3 (no stored
+trajectory uses the NN model); the two meet only through the 6-vector of coefficients
+(aircraft.py:269-277), which is the same code for every model.  The quaternion normalisation
+switch and the Jacobians are checked by properties / central differences only.
 
 All functions are batched over leading dimensions: x[...,13], u[...,7].
 State order  x = [p_ned(3), v_ned(3), q_frd_ned xyzw(4), omega_frd(3)]   (base.py:94-99)
@@ -116,7 +124,9 @@ class OracleConfig:
     substeps: int = 1                  # physical_integration_substeps (reference default 10)
     normalise: bool = False            # base.py:33 ; control/base.py:182-185
     stall_scaling: bool = False        # aircraft.py:30
-    coeff_model: str = "nn"            # 'nn' | 'default' (fixture)
+    coeff_model: str = "nn"            # 'nn' | 'default' (fixture) | 'poly' (fixture: pins Phi on the reference's stored trajectory)
+    rudder_moment_arm: float = 0.5     # utils.py:215 (AircraftConfiguration default; absent from the JSON)
+    poly_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "poly_model.npz")
     legacy_thrust: bool = False        # todo.md era: forces += thrust (now commented, aircraft.py:320)
     weights: Path | str = field(default=DEFAULT_WEIGHTS)
 
@@ -145,6 +155,12 @@ class AircraftOracle:
         self.com = torch.tensor([x, y, z], dtype=F64)
         self.g = torch.tensor(list(c.gravity), dtype=F64)
         self.nn = SurrogateF64(c.weights) if c.coeff_model == "nn" else None
+        if c.coeff_model == "poly":   # tests/golden/make_poly_golden.py
+            import numpy as _np
+            d = _np.load(c.poly_path)
+            self.poly_powers = torch.tensor(d["powers"], dtype=torch.int64)      # [34, 4] over (alpha, beta, aileron, elevator)
+            self.poly_coef = torch.tensor(d["coef"], dtype=F64)                  # [6, 34]
+            self.poly_icpt = torch.tensor(d["intercept"], dtype=F64)             # [6]
 
     # ---- aero-angle helpers (base.py:147-177, 229-241)
     def v_frd_rel(self, x: torch.Tensor) -> torch.Tensor:
@@ -181,6 +197,22 @@ class AircraftOracle:
             # coefficient_models.py:102-103
             cn = C[..., 5] + (-0.1) * 6 * rud * math.pi / 180
             C = torch.cat([C[..., :5], cn[..., None]], dim=-1)
+        elif self.cfg.coeff_model == "poly":   # PolynomialModel, coefficient_models.py:106-135
+            eps, b, arm = self.cfg.epsilon, self.cfg.span, self.cfg.rudder_moment_arm
+            uu, vv, ww = vb[..., 0], vb[..., 1], vb[..., 2]
+            p, qq, r = x[..., 10], x[..., 11], x[..., 12]
+            zero = torch.zeros_like(alpha)
+            a_el = torch.atan2(ww + arm * qq, uu + eps)                      # aircraft.py:189-199
+            a_lw = torch.atan2(ww - b * p / 4, uu + eps)                     # aircraft.py:202-211
+            a_rw = torch.atan2(ww + b * p / 4, uu + eps)                     # aircraft.py:213-222
+            vr = vv - arm * r                                               # aircraft.py:224-233
+            b_rud = torch.asin(vr / torch.sqrt(uu * uu + vr * vr + ww * ww + eps))
+            out = self._poly(alpha, beta, ail, ele)
+            lw, rw = self._poly(a_lw, zero, zero, zero), self._poly(a_rw, zero, zero, zero)
+            cl = out[..., 3] + b / 4 * (rw[..., 2] / 2 - lw[..., 2] / 2)
+            cm = self._poly(a_el, beta, ail, ele)[..., 4]
+            cn = self._poly(alpha, b_rud, ail, ele)[..., 5] + 0.01 * 6 * rud * math.pi / 180
+            C = torch.stack([out[..., 0], out[..., 1], out[..., 2], cl, cm, cn], dim=-1)
         else:  # DefaultModel, coefficient_models.py:41-78
             p, qq, r = x[..., 10], x[..., 11], x[..., 12]
             CD = 0.02 + 0.3 * alpha ** 2
@@ -199,6 +231,13 @@ class AircraftOracle:
         c[0] = c[0] + (-0.1) * flaps      # aircraft.py:297-299
         c[2] = c[2] + (-0.6) * flaps
         return torch.stack(c, dim=-1)
+
+    def _poly(self, alpha, beta, ail, ele):
+        """intercept + coef . monomials(alpha, beta, aileron, elevator): the CasADi functions that
+        main/surrogates/polynomial_model.py:76-104 generates from the stored sklearn fit."""
+        z = torch.stack([alpha, beta, ail, ele], dim=-1)                       # [..., 4]
+        mono = (z[..., None, :] ** self.poly_powers).prod(-1)                   # [..., 34]
+        return mono @ self.poly_coef.T + self.poly_icpt
 
     # ---- forces and moments (aircraft.py:309-330 ; base.py:253-278)
     def forces_frd(self, x, u):
