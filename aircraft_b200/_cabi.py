@@ -10,7 +10,8 @@ from pathlib import Path
 NX, NU = 13, 7
 LAYOUT_SOA, LAYOUT_AOS = 0, 1
 FLAG_NORMALISE, FLAG_SHARED_U = 1, 2
-OK, EINVAL, ECUDA, ENODEV, ENOMEM = 0, -1, -2, -3, -4
+OK, EINVAL, ECUDA, ENODEV, ENOMEM, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
+MODEL_POLY, MODEL_LINEAR, MODEL_DEFAULT = 1, 2, 3
 
 LIB_NAME = "libaircraft_b200.so"
 LIB_PATH = Path(__file__).resolve().parent / LIB_NAME
@@ -76,6 +77,7 @@ PROTOTYPES = {
     "airc_create": (C.c_int, [_PP, _NP, _i32, C.POINTER(_vp)]),
     "airc_destroy": (C.c_int, [_vp]),
     "airc_last_error": (C.c_char_p, [_vp]),
+    "airc_create_model": (C.c_int, [_PP, _i32, _vp, _i32, _i32, C.POINTER(_vp)]),
     "airc_state_derivative": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp]),
     "airc_diagnostics": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp, _vp]),
     "airc_diagnostics_host": (C.c_int, [_vp, _vp, _vp, _i64, _i32, _vp]),

@@ -29,7 +29,8 @@ from . import _cabi
 from ._cabi import (FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX, NZ)
 from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH)
-from .params import load_nn_blob, make_cost_params, make_params, make_sweep_params
+from .params import (load_linear_model, load_nn_blob, load_poly_model, make_cost_params, make_params,
+                     make_sweep_params)
 
 try:  # torch is plumbing (device memory, streams); the numpy/host path does not need it
     import torch
@@ -56,21 +57,52 @@ class NeuralModel(CoefficientModel):
         self.aircraft = aircraft
 
 
-def _unsupported(kind: str) -> Callable:
-    def factory(path, aircraft, **kw):
-        raise NotImplementedError(
-            f"coeff_model_type='{kind}' is outside the B200 hot path (SURVEY.md section 8a: only "
-            "the 'nn' surrogate is served); use the reference for this model")
-    return factory
+class _TableModel(CoefficientModel):
+    """The registry's other models (coefficient_models.py:41-135) as parameter tables for
+    airc_create_model.  They are served by the one-node-per-thread kernels (state_derivative,
+    state_update, rollout, diagnostics); linearize / lagrangian_hessian / defects / sweep exist for
+    'nn' only and raise on these."""
+    blob = None
+    model_id = 0
+
+    def __init__(self, table: Optional[np.ndarray], aircraft: "Aircraft"):
+        self.table = table
+        self.aircraft = aircraft
 
 
-# same keys as the reference's registry; unknown keys fall back to 'default' there
-# (aircraft.py:37), which this build refuses loudly instead of silently changing the model.
+class PolynomialModel(_TableModel):
+    """'poly' (coefficient_models.py:106-135): what the reference's MPC / MHTT / RL / simulation scripts
+    run with.  Reads the reference's own pickle without CasADi (params.load_poly_model)."""
+    model_id = _cabi.MODEL_POLY
+
+    def __init__(self, path, aircraft):
+        arm = getattr(aircraft.opts.aircraft_config, "rudder_moment_arm", 0.5)
+        super().__init__(load_poly_model(path, arm), aircraft)
+
+
+class LinearModel(_TableModel):
+    """'linear' (coefficient_models.py:80-89) from data/networks/linearised.csv."""
+    model_id = _cabi.MODEL_LINEAR
+
+    def __init__(self, path, aircraft):
+        super().__init__(load_linear_model(path), aircraft)
+
+
+class DefaultModel(_TableModel):
+    """'default' (coefficient_models.py:41-78): constants as written in the reference."""
+    model_id = _cabi.MODEL_DEFAULT
+
+    def __init__(self, aircraft):
+        super().__init__(None, aircraft)
+
+
+# same keys as the reference's registry.  Unknown keys fall back to 'default' there (aircraft.py:37);
+# this build refuses them loudly instead of silently changing the model.
 COEFF_MODEL_REGISTRY: Dict[str, Callable] = {
     "nn": lambda path, aircraft, **kw: NeuralModel(path, aircraft, realtime=kw.get("realtime", False)),
-    "linear": _unsupported("linear"),
-    "poly": _unsupported("poly"),
-    "default": _unsupported("default"),
+    "linear": lambda path, aircraft, **kw: LinearModel(path, aircraft),
+    "poly": lambda path, aircraft, **kw: PolynomialModel(path, aircraft),
+    "default": lambda path, aircraft, **kw: DefaultModel(aircraft),
 }
 
 
@@ -168,10 +200,11 @@ class Aircraft:
 
     @classmethod
     def from_problem(cls, path: Path | str = DEFAULT_PROBLEM_PATH, *, com=None, device=None,
-                     normalise: bool = False, coeff_model_path: Path | str = "", **opts_kw):
-        """Aircraft from the ``"aircraft"`` block of problem_definition.json with the 'nn' model,
+                     normalise: bool = False, coeff_model_path: Path | str = "",
+                     coeff_model_type: str = "nn", **opts_kw):
+        """Aircraft from the ``"aircraft"`` block of problem_definition.json (default: the 'nn' model),
         as the reference's scripts build it (main/control/control.py:159-167)."""
-        opts = AircraftOpts(coeff_model_type="nn", coeff_model_path=coeff_model_path,
+        opts = AircraftOpts(coeff_model_type=coeff_model_type, coeff_model_path=coeff_model_path,
                             aircraft_config=AircraftConfiguration.from_json(path), **opts_kw)
         return cls(opts, com=com, device=device, normalise=normalise)
 
@@ -232,8 +265,14 @@ class Aircraft:
                                  epsilon=self.epsilon, stall_scaling=self._stall_scaling)
             params.mass = float(self.mass)
             h = C.c_void_p()
-            rc = self._lib.airc_create(C.byref(params), C.byref(self.coefficient_model.blob),
-                                       self._device, C.byref(h))
+            cm = self.coefficient_model
+            if cm.blob is not None:
+                rc = self._lib.airc_create(C.byref(params), C.byref(cm.blob), self._device, C.byref(h))
+            else:
+                tab = cm.table
+                rc = self._lib.airc_create_model(C.byref(params), cm.model_id,
+                                                 None if tab is None else tab.ctypes.data,
+                                                 0 if tab is None else int(tab.size), self._device, C.byref(h))
             _check(rc, self._lib, "airc_create")
             self._handle = h
         return self._handle

@@ -106,6 +106,30 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   return AIRC_OK;
 }
 
+int airc_create_model(const AircParams* params, int model, const float* model_params, int n_model_params,
+                      int device, AircHandle** out) {
+  if (!params || !out) return fail(AIRC_EINVAL, "airc_create_model: NULL argument%s", "");
+  const int want = model == AIRC_MODEL_POLY ? 6 * (NPOLY + 1) + 1 : (model == AIRC_MODEL_LINEAR ? 36 : 0);
+  if ((model != AIRC_MODEL_POLY && model != AIRC_MODEL_LINEAR && model != AIRC_MODEL_DEFAULT) ||
+      n_model_params != want || (want && !model_params))
+    return fail(AIRC_EINVAL, "airc_create_model: unknown model or wrong parameter count%s", "");
+  static_assert(AIRC_MODEL_POLY == AIRC_MODEL_POLY_ && AIRC_MODEL_LINEAR == AIRC_MODEL_LINEAR_ &&
+                AIRC_MODEL_DEFAULT == AIRC_MODEL_DEFAULT_, "header and kernels disagree on the model ids");
+  AircNNBlob* dummy = new (std::nothrow) AircNNBlob;   // airc_create wants a network; its storage is then reused
+  if (!dummy) return fail(AIRC_ENOMEM, "airc_create_model: out of host memory%s", "");
+  memset(dummy, 0, sizeof(*dummy));
+  for (int i = 0; i < 5; ++i) dummy->input_std[i] = 1.0f;
+  for (int i = 0; i < 6; ++i) dummy->output_std[i] = 1.0f;
+  AircHandle* h = nullptr;
+  const int rc = airc_create(params, dummy, device, &h);
+  delete dummy;
+  if (rc) return rc;
+  build_devconst_model(*params, model, model_params, h->dc);
+  h->packed = 0;
+  *out = h;
+  return AIRC_OK;
+}
+
 int airc_destroy(AircHandle* h) {
   if (!h) return AIRC_OK;
   {
@@ -126,7 +150,8 @@ int airc_state_derivative(const AircHandle* h, const float* x, const float* u, i
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
   NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(xdot, n, 13, layout), nullptr, 0.f, n, 1, 0};
   const int bs = 128;
-  state_derivative_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  if (h->dc.model) state_derivative_kernel<1><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  else state_derivative_kernel<0><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
   return check_launch();
 }
 
@@ -140,7 +165,8 @@ int airc_diagnostics(const AircHandle* h, const float* x, const float* u, int64_
   NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(out, n, AIRC_NDIAG, layout), nullptr, 0.f, n, 1, 0};
   static_assert(AIRC_NDIAG == NDIAG, "header and kernel disagree on the diagnostics record");
   const int bs = 128;
-  diagnostics_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  if (h->dc.model) diagnostics_kernel<1><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  else diagnostics_kernel<0><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
   return check_launch();
 }
 
@@ -156,7 +182,8 @@ int airc_state_update(const AircHandle* h, const float* x, const float* u, float
   NodeArgs a{view(x, n, 13, layout), view(u, n, 7, layout), viewW(x_next, n, 13, layout),
              dt_per_node, dt, n, substeps, (int)(flags & AIRC_FLAG_NORMALISE)};
   const int bs = (n <= 148 * 64) ? 32 : 128;
-  state_update_kernel<<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  if (h->dc.model) state_update_kernel<1><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  else state_update_kernel<0><<<(unsigned)((n + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
   return check_launch();
 }
 
@@ -198,6 +225,13 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
   // kernel's finer wave granularity wins (profiles/r1_variants_packed.txt).  AIRC_ROLLOUT_IMPL=1|2
   // forces one of them (A/B timing).
   const long long wave2 = (long long)h->sm_count * 3 * AIRC_R2_BS * 2;
+  if (h->dc.model) {   // poly / linear / default coefficient models: one-trajectory kernel only
+    if (cost && X) rollout_kernel<true, true, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    else if (cost) rollout_kernel<true, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    else if (X) rollout_kernel<false, true, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    else rollout_kernel<false, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    return check_launch();
+  }
   if (h->packed == 2 || (h->packed == 1 && B >= 2 * wave2)) {
     const unsigned grid2 = (unsigned)((B + 2 * AIRC_R2_BS - 1) / (2 * AIRC_R2_BS));
     if (cost && X) rollout2_kernel<true, true><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
@@ -220,6 +254,7 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
   if (!h || !x || !u || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_linearize: bad argument%s", "");
+  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_%s: derivatives are built for the 'nn' coefficient model only", "linearize");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
@@ -279,6 +314,7 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   if (!h || !x || !u || !lam || !H || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_hessian: bad argument%s", "");
+  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_%s: derivatives are built for the 'nn' coefficient model only", "hessian");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
@@ -394,6 +430,7 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
   if (!h || !x0 || (!U_nom && H > 0) || !sp || !cp || !record || B < 0 || B > 0xFFFFFFFFLL || H < 0 ||
       substeps < 1 || (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_sweep: bad argument%s", "");
+  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_sweep: the sampling sweep is built for the 'nn' coefficient model only%s", "");
   const int C = ckpt_interval_of(H, sp->ckpt_interval);
   const int S = H > 0 ? (H + C - 1) / C : 1;
   const size_t need_min = 256;

@@ -85,6 +85,7 @@ struct NetCoop {
       J[k][0] = a.hi; J[k][1] = b.lo; J[k][2] = b.hi; J[k][3] = d.lo; J[k][4] = d.hi;
     }
   }
+  AIRC_HD void adjust(const DevConst&, Stage&, const float*, const Ctl&) const {}
 };
 
 template <class T>

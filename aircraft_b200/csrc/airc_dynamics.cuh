@@ -55,6 +55,7 @@ struct DevConst {
   float k_flap_x;     // -0.1            (aircraft.py:297-299)
   float k_flap_z;     // -0.6
   int stall_scaling;
+  int model;           // 0 nn | AIRC_MODEL_* (airc_alt.cuh): then `net` holds AltParams instead of the network
 };
 
 // control inputs that the NN path actually reads (thrust is inert, aircraft.py:320)
@@ -177,6 +178,8 @@ struct NetFull {
   AIRC_HD void eval(float qbar, float alpha, float beta, const Ctl& c, float C[6], float J[6][5]) const {
     surrogate<WITH_JAC>(*net, qbar, alpha, beta, c, C, J);
   }
+  // hook for coefficient models that also read the body rates (airc_alt.cuh); the NN model does not
+  AIRC_HD void adjust(const DevConst&, Stage&, const float*, const Ctl&) const {}
 };
 
 // f(x,u) without the trivial p_dot = v rows.  base.py:385-406.
@@ -210,6 +213,7 @@ AIRC_HD void f_eval_net(const DevConst& P, const Net& net, const float v[3], con
   }
 
   net.template eval<WITH_JAC>(s.qbar, s.alpha, s.beta, c, s.C, J);
+  net.adjust(P, s, w, c);
   s.C[5] = fmaf(P.k_rudder, c.dr, s.C[5]);                  // coefficient_models.py:102-103
   s.sa = 1.0f;
   s.sbeta_s = 1.0f;
@@ -264,11 +268,18 @@ AIRC_HD void f_eval_net(const DevConst& P, const Net& net, const float v[3], con
     wdot[i] = fmaf(P.Iinv[3 * i + 2], t[2], fmaf(P.Iinv[3 * i + 1], t[1], P.Iinv[3 * i] * t[0]));
 }
 
-template <bool WITH_JAC>
+}  // namespace airc
+#include "airc_alt.cuh"
+namespace airc {
+
+// MODEL 0: the NN surrogate (every tuned kernel); MODEL 1: the registry's other coefficient models
+// (airc_alt.cuh), primal only.
+template <bool WITH_JAC, int MODEL = 0>
 AIRC_HD void f_eval(const DevConst& P, const float v[3], const float q[4], const float w[3],
                     const Ctl& c, float vdot[3], float qdot[4], float wdot[3], Stage& s,
                     float J[6][5]) {
-  f_eval_net<WITH_JAC>(P, NetFull{&P.net}, v, q, w, c, vdot, qdot, wdot, s, J);
+  if constexpr (MODEL == 0) f_eval_net<WITH_JAC>(P, NetFull{&P.net}, v, q, w, c, vdot, qdot, wdot, s, J);
+  else f_eval_net<false>(P, NetAlt{&alt_params(P)}, v, q, w, c, vdot, qdot, wdot, s, J);
 }
 
 // Directional derivative of f at the point described by (v,q,w,c,s,J) along

@@ -70,4 +70,28 @@ inline void build_devconst(const AircParams& p, const AircNNBlob& nn, DevConst& 
   d.stall_scaling = p.stall_scaling;
 }
 
+// DevConst for one of the registry's other coefficient models (airc_alt.cuh): the network's storage
+// holds the model's parameter table.  model_params as documented at airc_create_model.
+inline void build_devconst_model(const AircParams& p, int model, const float* model_params, DevConst& d) {
+  AircNNBlob* dummy = new AircNNBlob;
+  memset(dummy, 0, sizeof(*dummy));
+  for (int i = 0; i < 5; ++i) dummy->input_std[i] = 1.0f;
+  for (int i = 0; i < 6; ++i) dummy->output_std[i] = 1.0f;
+  build_devconst(p, *dummy, d);
+  delete dummy;
+  AltParams ap;
+  memset(&ap, 0, sizeof(ap));
+  ap.span = (float)p.span;
+  ap.k_rudder_model = (float)((model == AIRC_MODEL_POLY_ ? 0.01 : -0.1) * 6.0 * M_PI / 180.0);
+  if (model == AIRC_MODEL_POLY_) {
+    memcpy(ap.poly, model_params, sizeof(ap.poly));
+    ap.arm = model_params[6 * (NPOLY + 1)];
+  } else if (model == AIRC_MODEL_LINEAR_) {
+    memcpy(ap.lin, model_params, sizeof(ap.lin));
+  }
+  memset(&d.net, 0, sizeof(d.net));
+  memcpy(&d.net, &ap, sizeof(ap));
+  d.model = model;
+}
+
 }  // namespace airc

@@ -72,6 +72,7 @@ struct NodeArgs {
   int normalise;
 };
 
+template <int MODEL>
 __global__ void __launch_bounds__(128)
 state_derivative_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -82,12 +83,13 @@ state_derivative_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   State d;
   Stage st;
   float J[6][5];
-  f_eval<false>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
+  f_eval<false, MODEL>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
 #pragma unroll
   for (int k = 0; k < 3; ++k) d.p[k] = s.v[k];
   store_state(a.out, i, d);
 }
 
+template <int MODEL>
 __global__ void __launch_bounds__(128)
 state_update_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -96,7 +98,7 @@ state_update_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   load_state(a.x, i, s);
   const Ctl c = load_ctl(a.u.base + i * a.u.sb, a.u.sc);
   const float dt = a.dt_per_node ? __ldg(a.dt_per_node + i) : a.dt;
-  state_update<0>(P, s, c, dt, a.substeps, a.normalise != 0, nullptr);
+  state_update<0, MODEL>(P, s, c, dt, a.substeps, a.normalise != 0, nullptr);
   store_state(a.out, i, s);
 }
 
@@ -110,6 +112,7 @@ state_update_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
 //   out[5]    beta             base.py:229-235        out[19:22] phi, theta, psi base.py:179-197
 //   out[6]    qbar             base.py:237-241
 constexpr int NDIAG = 22;
+template <int MODEL>
 __global__ void __launch_bounds__(128)
 diagnostics_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -120,7 +123,7 @@ diagnostics_kernel(const __grid_constant__ DevConst P, const NodeArgs a) {
   State d;
   Stage st;
   float J[6][5];
-  f_eval<false>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
+  f_eval<false, MODEL>(P, s.v, s.q, s.w, c, d.v, d.q, d.w, st, J);
   float o[NDIAG];
   const float vb2 = fmaf(st.vb[2], st.vb[2], fmaf(st.vb[1], st.vb[1], st.vb[0] * st.vb[0]));
   float V, rV;
@@ -190,7 +193,7 @@ AIRC_D float body_speed2(const DevConst& P, const State& s) {
 #ifndef AIRC_ROLLOUT_BS
 #define AIRC_ROLLOUT_BS 128
 #endif
-template <bool COST, bool TRAJ>
+template <bool COST, bool TRAJ, int MODEL = 0>
 __global__ void __launch_bounds__(AIRC_ROLLOUT_BS, AIRC_ROLLOUT_MINBLOCKS)
 rollout_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
   const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -226,7 +229,7 @@ rollout_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
       for (int i = 0; i < 7; ++i) up[i] = un[i];
       sum_v2 += body_speed2(P, s);
     }
-    state_update<0>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
+    state_update<0, MODEL>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
     if (TRAJ) {
       const VecViewW Xk{Xb + (long long)(k + 1) * a.X_sk, 0, a.X_sc};
       store_state(Xk, 0, s);

@@ -20,7 +20,7 @@ struct Tangent {
   Ctl dc;
 };
 
-template <int NT>
+template <int NT, int MODEL = 0>
 AIRC_HD void rk4_step(const DevConst& P, State& x, const Ctl& c, float h, Tangent* T) {
   const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
   // stage state (v,q,w only: f does not read p) and accumulators
@@ -52,7 +52,7 @@ AIRC_HD void rk4_step(const DevConst& P, State& x, const Ctl& c, float h, Tangen
     float kv[3], kq[4], kw[3];
     Stage s;
     float J[6][5];
-    f_eval<(NT > 0)>(P, sv, sq, sw, c, kv, kq, kw, s, J);
+    f_eval<(NT > 0), MODEL>(P, sv, sq, sw, c, kv, kq, kw, s, J);
     // tangents first: they need the stage state before it is overwritten
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
@@ -124,11 +124,12 @@ AIRC_HD void normalise_q(State& x, Tangent* T) {
 }
 
 // Phi(x,u,dt) of base.py:450-480: n substeps of h = dt/n without normalisation, one at the end.
-template <int NT>
+template <int NT, int MODEL = 0>
 AIRC_HD void state_update(const DevConst& P, State& x, const Ctl& c, float dt, int substeps,
                           bool normalise, Tangent* T) {
+  static_assert(NT == 0 || MODEL == 0, "tangents exist for the NN model only");
   const float h = (substeps == 1) ? dt : dt / (float)substeps;
-  for (int s = 0; s < substeps; ++s) rk4_step<NT>(P, x, c, h, T);
+  for (int s = 0; s < substeps; ++s) rk4_step<NT, MODEL>(P, x, c, h, T);
   if (normalise) normalise_q<NT>(x, T);
 }
 

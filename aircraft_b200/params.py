@@ -98,3 +98,75 @@ def make_sweep_params(seed: int = 0, index_offset: int = 0, sigma0=(1.0, 1.0, 1.
     s.hi[:] = [float(v) for v in hi]
     s.ckpt_interval = int(ckpt_interval)
     return s
+
+
+# ---------------------------------------------------------------------------------------------
+# The registry's other coefficient models (coefficient_models.py:41-135), for airc_create_model.
+NPOLY = 34
+
+
+def _canonical_powers():
+    """sklearn PolynomialFeatures(degree=3, include_bias=False) exponents for 4 inputs, in order."""
+    import itertools
+    rows = []
+    for deg in (1, 2, 3):
+        for comb in itertools.combinations_with_replacement(range(4), deg):
+            e = [0, 0, 0, 0]
+            for i in comb:
+                e[i] += 1
+            rows.append(e)
+    return np.asarray(rows, np.int64)
+
+
+class _PickleStub:
+    def __init__(self, *a, **k):
+        pass
+
+    def __setstate__(self, state):
+        self.state = state
+
+
+def load_poly_model(path, rudder_moment_arm: float = 0.5) -> np.ndarray:
+    """float32[211] for AIRC_MODEL_POLY from the reference's data/networks/fitted_models_casadi.pkl
+    (main/surrogates/polynomial_model.py:228-271) or from a .npz with powers/coef/intercept
+    (tests/golden/make_poly_golden.py).  The pickle's CasADi Functions are generated from the very
+    numbers stored next to them ('fitted_models': coef, intercept), so CasADi and sklearn objects are
+    replaced by stubs while unpickling and only the plain arrays are read."""
+    import pickle
+    path = Path(path)
+    if path.suffix == ".npz":
+        d = np.load(path)
+        powers, coef, icpt = d["powers"], d["coef"], d["intercept"]
+    else:
+        class U(pickle.Unpickler):
+            def find_class(self, module, name):
+                if module.split(".")[0] in ("casadi", "sklearn"):
+                    return type(name, (_PickleStub,), {"__module__": module})
+                return super().find_class(module, name)
+        with open(path, "rb") as f:
+            fm = U(f).load()["fitted_models"]
+        names = ["CX", "CY", "CZ", "Cl", "Cm", "Cn"]
+        if list(fm) != names:
+            raise RuntimeError(f"unexpected coefficient names in {path}: {list(fm)}")
+        coef = np.stack([np.asarray(fm[k]["coef"], np.float64).reshape(-1) for k in names])
+        icpt = np.array([float(fm[k]["intercept"]) for k in names])
+        st = getattr(fm["CX"]["poly"], "state", {}) or {}
+        if st.get("degree", 3) != 3 or st.get("include_bias", False) or st.get("n_features_in_", 4) != 4 or \
+                st.get("interaction_only", False):
+            raise RuntimeError(f"{path}: not the degree-3, 4-input, bias-free polynomial this build evaluates")
+        powers = _canonical_powers()
+    if coef.shape != (6, NPOLY) or not np.array_equal(np.asarray(powers), _canonical_powers()):
+        raise RuntimeError(f"{path}: monomial set differs from degree-3 PolynomialFeatures over 4 inputs")
+    out = np.empty(6 * (NPOLY + 1) + 1, np.float32)
+    out[:-1] = np.concatenate([coef, icpt[:, None]], axis=1).reshape(-1)
+    out[-1] = rudder_moment_arm
+    return out
+
+
+def load_linear_model(path) -> np.ndarray:
+    """float32[36] for AIRC_MODEL_LINEAR: the six rows of data/networks/linearised.csv
+    (q, alpha, beta, aileron, elevator, intercept), as LinearModel reads them (coefficient_models.py:80-84)."""
+    a = np.loadtxt(path, delimiter=",", skiprows=1, dtype=np.float64)
+    if a.shape != (6, 6):
+        raise RuntimeError(f"{path}: expected a 6x6 coefficient table, got {a.shape}")
+    return a.astype(np.float32).reshape(-1)

@@ -43,6 +43,7 @@ extern "C" {
 #define AIRC_ECUDA (-2)    /* CUDA runtime error; text via airc_last_error() */
 #define AIRC_ENODEV (-3)   /* no usable sm_100 device */
 #define AIRC_ENOMEM (-4)
+#define AIRC_EUNSUPPORTED (-5) /* entry point not built for this handle's coefficient model */
 
 /* layout of batched vectors */
 #define AIRC_LAYOUT_SOA 0  /* [13][B] / [H][7][B]: batch index fastest -- the native layout; it is
@@ -111,6 +112,24 @@ const char* airc_build_info(void);
 
 /* Create a handle for CUDA device `device`.  `nn` may be a HOST pointer only. */
 int airc_create(const AircParams* params, const AircNNBlob* nn, int device, AircHandle** out);
+
+/* The registry's other coefficient models (src/aircraft/dynamics/coefficient_models.py:32-37), for
+ * airc_state_derivative / airc_state_update / airc_rollout / airc_diagnostics (and their _host
+ * variants).  The Jacobian, Hessian, defect and sampling-sweep entry points return AIRC_EUNSUPPORTED
+ * on such a handle.
+ *   AIRC_MODEL_POLY     PolynomialModel (coefficient_models.py:106-135; the model of main/control/control.py:166,
+ *                       main/mhe/mhtt.py:49, main/rl/rl.py:36).  model_params: float[6][35] = per coefficient
+ *                       (CX CY CZ Cl Cm Cn) the 34 weights of the degree-3 monomials of (alpha, beta, aileron,
+ *                       elevator) in sklearn PolynomialFeatures order, then the intercept
+ *                       (main/surrogates/polynomial_model.py:76-104); then rudder_moment_arm (utils.py:215).  n = 211.
+ *   AIRC_MODEL_LINEAR   LinearModel (coefficient_models.py:80-89).  model_params: float[6][6], rows of
+ *                       data/networks/linearised.csv (q, alpha, beta, aileron, elevator, intercept).  n = 36.
+ *   AIRC_MODEL_DEFAULT  DefaultModel (coefficient_models.py:41-78), constants as written there.  n = 0.   */
+#define AIRC_MODEL_POLY 1
+#define AIRC_MODEL_LINEAR 2
+#define AIRC_MODEL_DEFAULT 3
+int airc_create_model(const AircParams* params, int model, const float* model_params, int n_model_params,
+                      int device, AircHandle** out);
 int airc_destroy(AircHandle* h);
 const char* airc_last_error(const AircHandle* h);
 

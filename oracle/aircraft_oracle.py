@@ -126,6 +126,7 @@ class OracleConfig:
     stall_scaling: bool = False        # aircraft.py:30
     coeff_model: str = "nn"            # 'nn' | 'default' (fixture) | 'poly' (fixture: pins Phi on the reference's stored trajectory)
     rudder_moment_arm: float = 0.5     # utils.py:215 (AircraftConfiguration default; absent from the JSON)
+    linear_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "linearised.csv")
     poly_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "poly_model.npz")
     legacy_thrust: bool = False        # todo.md era: forces += thrust (now commented, aircraft.py:320)
     weights: Path | str = field(default=DEFAULT_WEIGHTS)
@@ -155,6 +156,9 @@ class AircraftOracle:
         self.com = torch.tensor([x, y, z], dtype=F64)
         self.g = torch.tensor(list(c.gravity), dtype=F64)
         self.nn = SurrogateF64(c.weights) if c.coeff_model == "nn" else None
+        if c.coeff_model == "linear":  # the six rows of data/networks/linearised.csv (copied to tests/golden/)
+            import numpy as _np
+            self.lin = torch.tensor(_np.loadtxt(c.linear_path, delimiter=",", skiprows=1), dtype=F64)
         if c.coeff_model == "poly":   # tests/golden/make_poly_golden.py
             import numpy as _np
             d = _np.load(c.poly_path)
@@ -213,6 +217,11 @@ class AircraftOracle:
             cm = self._poly(a_el, beta, ail, ele)[..., 4]
             cn = self._poly(alpha, b_rud, ail, ele)[..., 5] + 0.01 * 6 * rud * math.pi / 180
             C = torch.stack([out[..., 0], out[..., 1], out[..., 2], cl, cm, cn], dim=-1)
+        elif self.cfg.coeff_model == "linear":   # LinearModel, coefficient_models.py:80-89
+            inp = torch.stack([qbar, alpha, beta, ail, ele, torch.ones_like(alpha)], dim=-1)
+            C = inp @ self.lin.T
+            cn = C[..., 5] + (-0.1) * 6 * rud * math.pi / 180
+            C = torch.cat([C[..., :5], cn[..., None]], dim=-1)
         else:  # DefaultModel, coefficient_models.py:41-78
             p, qq, r = x[..., 10], x[..., 11], x[..., 12]
             CD = 0.02 + 0.3 * alpha ** 2

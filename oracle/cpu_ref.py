@@ -174,6 +174,24 @@ class HostEmul:
                                        substeps, 1 if normalise else 0, xn, A, Bm)
         return xn, A, Bm
 
+    def model_state_update(self, model, table, x, u, dt, substeps=1, normalise=False):
+        """airc_alt.cuh (poly / linear / default coefficient models) through the product's RK4."""
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        out = np.empty_like(x)
+        self.lib.emul_model_state_update.argtypes = [_PP, C.c_int, C.c_void_p, _f32, _f32, C.c_float, C.c_int64,
+                                                     C.c_int, C.c_uint32, _f32]
+        self.lib.emul_model_state_update(C.byref(self.params), model, None if table is None else table.ctypes.data,
+                                         x, u, float(dt), x.shape[0], substeps, 1 if normalise else 0, out)
+        return out
+
+    def model_state_derivative(self, model, table, x, u):
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        out = np.empty_like(x)
+        self.lib.emul_model_state_derivative.argtypes = [_PP, C.c_int, C.c_void_p, _f32, _f32, C.c_int64, _f32]
+        self.lib.emul_model_state_derivative(C.byref(self.params), model, None if table is None else table.ctypes.data,
+                                             x, u, x.shape[0], out)
+        return out
+
     def hessian(self, x, u, lam, dt, substeps=1, normalise=False):
         """K3 arithmetic (airc_hess.cuh) on the host: H[n,21,21], grad[n,21], value[n]."""
         x, u, lam = (np.ascontiguousarray(a, np.float32) for a in (x, u, lam))

@@ -153,6 +153,31 @@ void emul_linearize_packed_dt(const AircParams* p, const AircNNBlob* nn, const f
   linearize_packed_impl(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, Dt);
 }
 
+// the registry's other coefficient models (airc_alt.cuh) through the product's f / RK4
+void emul_model_state_update(const AircParams* p, int model, const float* model_params, const float* x,
+                             const float* u, float dt, int64_t n, int substeps, uint32_t flags, float* xn) {
+  DevConst P;
+  build_devconst_model(*p, model, model_params, P);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    state_update<0, 1>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, nullptr);
+    store(s, xn + 13 * i);
+  }
+}
+void emul_model_state_derivative(const AircParams* p, int model, const float* model_params, const float* x,
+                                 const float* u, int64_t n, float* xdot) {
+  DevConst P;
+  build_devconst_model(*p, model, model_params, P);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c; Stage st; float J[6][5];
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* o = xdot + 13 * i;
+    f_eval<false, 1>(P, s.v, s.q, s.w, c, o + 3, o + 6, o + 10, st, J);
+    for (int k = 0; k < 3; ++k) o[k] = s.v[k];
+  }
+}
+
 // K3 arithmetic (airc_hess.cuh): the 64 (outer, inner-pair) tasks of a node, one after the other.
 // H[n][21][21] (zero-filled here), grad[n][21], value[n]
 void emul_hessian(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,
