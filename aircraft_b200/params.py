@@ -136,6 +136,8 @@ def load_poly_model(path, rudder_moment_arm: float = 0.5) -> np.ndarray:
     path = Path(path)
     if path.suffix == ".npz":
         d = np.load(path)
+        if not {"powers", "coef", "intercept"} <= set(d.files):
+            raise RuntimeError(f"{path}: not a polynomial-model table (powers, coef, intercept)")
         powers, coef, icpt = d["powers"], d["coef"], d["intercept"]
     else:
         class U(pickle.Unpickler):

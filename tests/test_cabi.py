@@ -87,8 +87,17 @@ def test_facade_mirrors_reference_interface(built):
     ac.com = TRIM_COM           # scripts assign after construction (main/control/control.py:168-172)
     assert ac.com == tuple(TRIM_COM)
     assert AircraftOpts().physical_integration_substeps == 10       # base.py:12
+    # the registry's other models are tables behind airc_create_model; unknown keys are refused, not defaulted
+    gold = ROOT / "tests" / "golden"
+    pm = Aircraft(AircraftOpts(coeff_model_type="poly", coeff_model_path=gold / "poly_model.npz", aircraft_config=cfg))
+    assert pm.coefficient_model.table.shape == (211,) and pm.coefficient_model.model_id == 1
+    lm = Aircraft(AircraftOpts(coeff_model_type="linear", coeff_model_path=gold / "linearised.csv", aircraft_config=cfg))
+    assert lm.coefficient_model.table.shape == (36,)
+    assert Aircraft(AircraftOpts(coeff_model_type="default", aircraft_config=cfg)).coefficient_model.table is None
+    with pytest.raises(RuntimeError):
+        Aircraft(AircraftOpts(coeff_model_type="poly", coeff_model_path=gold / "nn_golden.npz", aircraft_config=cfg))
     with pytest.raises(NotImplementedError):
-        Aircraft(AircraftOpts(coeff_model_type="poly", aircraft_config=cfg))
+        Aircraft(AircraftOpts(coeff_model_type="neural", aircraft_config=cfg))
     # shape errors are RuntimeError, as CasADi raises
     with pytest.raises(RuntimeError):
         ac.state_update(np.zeros(12), np.zeros(7), 0.01)
