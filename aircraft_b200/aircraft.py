@@ -112,6 +112,31 @@ class RolloutResult:
     trajectory: Any = None     # [B,H+1,13] (aos) or [H+1,13,B] (soa)
     cost: Any = None           # [B]
 
+    @property
+    def finite(self):
+        """Per-trajectory mask: final state (and cost) free of NaN/Inf.  NaNs propagate through the kernels
+        unchanged, as through CasADi; the reference's callers check for them (main/dynamics/dynamics.py:108)."""
+        ref = self.final if self.final is not None else self.trajectory
+        if ref is None:
+            ref = self.cost
+        is_t = _is_torch(ref)
+        fin = torch.isfinite if is_t else np.isfinite
+        B = self.cost.shape[0] if self.cost is not None else None
+        def per_traj(a):
+            if a is None:
+                return None
+            f = fin(a)
+            if f.ndim == 1:
+                return f
+            b_first = B is None or a.shape[0] == B          # aos: batch first; soa: batch last
+            axes = tuple(range(1, f.ndim)) if b_first else tuple(range(f.ndim - 1))
+            return f.all(dim=axes) if is_t else f.all(axis=axes)
+        parts = [m for m in (per_traj(self.final), per_traj(self.trajectory), per_traj(self.cost)) if m is not None]
+        out = parts[0]
+        for m in parts[1:]:
+            out = out & m
+        return out
+
 
 class SweepRecord:
     """The winner of a sampling sweep: views into the library's FP32 record

@@ -282,6 +282,10 @@ def run_native(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL writes its "NCCL version ..." banner to STDOUT at NCCL_DEBUG=VERSION (this image's setting);
+        # stdout must carry exactly one JSON line, so the banner level is lowered unless the caller asked for more
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"
         dist.init_process_group("nccl", device_id=dev)
     if world != args.gpus and rank == 0:
         print(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world}; using WORLD_SIZE", file=sys.stderr)
@@ -572,6 +576,26 @@ def side_measurements(torch, ac, dev, rank, args):
     out["c5_shard"] = {"workload": "BASELINE config 5 shard: 1024 windows x 50 nodes per GPU, A[.,13,13], B[.,13,7] (AoS)",
                        "value": n5 / (ms * 1e-3), "unit": "jacobian-evals/s", "ms_per_launch": ms,
                        "l2": "flushed between launches"}
+    # config 1: ONE trajectory x 100 steps (the reference's own CPU-runnable case): latency per step
+    x1 = torch.tensor(make_states(1, seed=1, level=True), dtype=torch.float32, device=dev)
+    U1 = device_control_sequences(torch, 1, 100, seed=11, device=dev).permute(2, 0, 1).contiguous()   # [1,100,7]
+    ms = time_launches(torch, lambda: ac.rollout(x1, U1, DT, return_trajectory=True), max(K, 20), 3, None)
+    out["c1"] = {"workload": "BASELINE config 1: 1 trajectory x 100 steps, full trajectory returned (latency case)",
+                 "value": ms * 1e3 / 100, "unit": "us/state-step", "higher_is_better": False, "ms_per_launch": ms}
+    if rank == 0:
+        try:
+            ref1 = _cpu_ref(1)
+            xs, Us = make_states(1, seed=1, level=True).astype(np.float64), U1.double().cpu().numpy()
+            ref1.rollout(xs, Us, DT)
+            t0 = time.perf_counter()
+            for _ in range(20):
+                ref1.rollout(xs, Us, DT)
+            out["c1"]["cpu_baseline"] = {"value": (time.perf_counter() - t0) / 20 / 100 * 1e6, "unit": "us/state-step",
+                                         "cores": 1, "kind": "port",
+                                         "sample": "20 repetitions of the same trajectory, oracle/cpu_ref.cpp float64"}
+        except Exception as e:  # the checker is optional for this side line
+            out["c1"]["cpu_baseline"] = {"unavailable": repr(e)}
+
     # row f.1: exact Lagrangian-Hessian blocks at the reference's horizon (298 nodes, todo.md tables) and in bulk
     for name, nh in (("hessian_298", 298), ("hessian_bulk", 262_144)):
         x = torch.tensor(make_states(nh, seed=600 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev).contiguous()

@@ -116,3 +116,16 @@ def test_product_never_imports_oracle():
         src = f.read_text()
         assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
         assert "oracle/" not in src.replace("oracle/host_emul.cpp", "") or f.suffix in (".cuh",), f
+
+
+def test_rollout_result_finite_mask():
+    from aircraft_b200.aircraft import RolloutResult
+    xf = np.zeros((5, 13)); xf[2, 4] = np.nan
+    cost = np.zeros(5); cost[4] = np.inf
+    r = RolloutResult(final=xf, cost=cost)
+    assert r.finite.tolist() == [True, True, False, True, False]
+    X = np.zeros((7, 13, 5)); X[3, 0, 1] = np.nan                     # soa trajectory: batch last
+    assert RolloutResult(trajectory=X, cost=np.zeros(5)).finite.tolist() == [True, False, True, True, True]
+    import torch
+    t = RolloutResult(final=torch.tensor(xf))
+    assert t.finite.tolist() == [True, True, False, True, True]
