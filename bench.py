@@ -346,14 +346,36 @@ def fp32_peak(ac):
     return float(tf.value)
 
 
-def rollout_roofline(kernel, tflops, peak, steps_per_launch, ms_kernel, ms_step, note=""):
+def ncu_traffic(kernel: str):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
+    capture of this workload (profiles/r1f_ncu_summary_sweep2.txt); None when the summary is not there."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    try:
+        rd = wr = None
+        hit = False
+        for ln in (ROOT / "profiles" / "r1f_ncu_summary_sweep2.txt").read_text().splitlines():
+            t = ln.split()
+            if ln.startswith("Kernel Name"):
+                hit = kernel in ln
+            elif hit and t and t[0] == "dram__bytes_read.sum" and rd is None:
+                rd = float(t[1].replace(",", "")) * unit[t[2]]
+            elif hit and t and t[0] == "dram__bytes_write.sum" and wr is None:
+                wr = float(t[1].replace(",", "")) * unit[t[2]]
+        return None if rd is None or wr is None else rd + wr
+    except Exception:
+        return None
+
+
+def rollout_roofline(kernel, tflops, peak, steps_per_launch, ms_kernel, ms_step, note="", traffic=None):
     return {"kernel": kernel, "bound": "fp32", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
             "frac": tflops / peak,
             "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); "
                            "MEASURED_PEAKS.json has no FP32 CUDA-core entry",
             "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": tflops / FP32_NOMINAL_TFLOPS,
             "flops_per_state_step": F_STEP, "state_steps_per_launch": steps_per_launch,
-            "kernel_ms": ms_kernel, "kernel_share_of_step": ms_kernel / ms_step, "traffic": None,
+            "kernel_ms": ms_kernel, "kernel_share_of_step": ms_kernel / ms_step, "traffic": traffic,
+            "traffic_unit": "bytes of DRAM read + write per launch (ncu --set full capture under profiles/); "
+                            "the kernel is FP32-bound, the traffic is the checkpoint / slice records",
             "note": note}
 
 
@@ -456,7 +478,8 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
         "best": {"min_cost": float(out.min_cost), "argmin": int(out.argmin)},
         "roofline": rollout_roofline("sweep2_kernel<ckpt> (+ sweep2_prep, sweep_winner2: < 2 % of the call)",
                                      roll_tflops, peak, per_gpu * H, ms_roll, ms_step,
-                                     "kernel_ms = CUDA events around the airc_sweep call (three launches)"),
+                                     "kernel_ms = CUDA events around the airc_sweep call (three launches)",
+                                     traffic=ncu_traffic("sweep2_kernel") if (per_gpu, H) == (C4_TOTAL // C4_GPUS, H_ROLL) else None),
     }
 
 
