@@ -59,9 +59,8 @@ class NeuralModel(CoefficientModel):
 
 class _TableModel(CoefficientModel):
     """The registry's other models (coefficient_models.py:41-135) as parameter tables for
-    airc_create_model.  They are served by the one-node-per-thread kernels (state_derivative,
-    state_update, rollout, diagnostics); linearize / lagrangian_hessian / defects / sweep exist for
-    'nn' only and raise on these."""
+    airc_create_model.  Everything but the sampling sweep is served: the primal entry points by the
+    one-node-per-thread kernels, linearize / defects / lagrangian_hessian by forward mode on jets."""
     blob = None
     model_id = 0
 

@@ -5,8 +5,9 @@
 //   AIRC_MODEL_LINEAR   LinearModel      coefficient_models.py:80-89
 //   AIRC_MODEL_DEFAULT  DefaultModel     coefficient_models.py:41-78
 // They plug into f_eval_net through the same policy interface as the network (eval + adjust) and are
-// served by the one-node-per-thread kernels (state_derivative, state_update, diagnostics, rollout);
-// the packed rollout, the sampling sweep, the Jacobian and the Hessian kernels are NN-only.
+// served by the one-node-per-thread kernels (state_derivative, state_update, diagnostics, rollout) and,
+// for derivatives, by the jets of airc_jet.cuh / airc_hess.cuh; the packed rollout, the sampling sweep and
+// the hand-derived tangents of K2 are NN-only.
 // Included from the middle of airc_dynamics.cuh (needs DevConst, Stage, Ctl).
 #pragma once
 

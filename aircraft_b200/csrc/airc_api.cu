@@ -254,7 +254,6 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
   if (!h || !x || !u || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_linearize: bad argument%s", "");
-  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_%s: derivatives are built for the 'nn' coefficient model only", "linearize");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
@@ -270,6 +269,12 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
   a.dt_per_node = dt_per_node; a.dt = dt; a.n = n; a.substeps = substeps;
   a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
   const int bs = 128;
+  if (h->dc.model) {   // poly / linear / default: two-column forward mode on jets (airc_hess.cuh)
+    const unsigned gridj = (unsigned)((n * 8 + bs - 1) / bs);
+    if (layout == AIRC_LAYOUT_SOA) linearize_jet_kernel<true, 1><<<gridj, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+    else linearize_jet_kernel<false, 1><<<gridj, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+    return check_launch();
+  }
 #ifdef AIRC_LIN_V1   // round-1 kernel: 16 lanes per node, everything recomputed per lane
   const long long threads = n * 16;
   linearize_kernel<<<(unsigned)((threads + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
@@ -314,7 +319,6 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   if (!h || !x || !u || !lam || !H || n < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
       (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_hessian: bad argument%s", "");
-  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_%s: derivatives are built for the 'nn' coefficient model only", "hessian");
   if (n == 0) return AIRC_OK;
   DeviceGuard g(h->device);
   if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
@@ -332,8 +336,11 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   const int bs = 128;
   const long long threads = n * HESS_LANES;
   const unsigned grid = (unsigned)((threads + bs - 1) / bs);
-  if (layout == AIRC_LAYOUT_SOA) hessian_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
-  else hessian_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+  if (h->dc.model) {
+    if (layout == AIRC_LAYOUT_SOA) hessian_kernel<true, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    else hessian_kernel<false, 1><<<grid, bs, 0, st>>>(h->dc, a);
+  } else if (layout == AIRC_LAYOUT_SOA) hessian_kernel<true, 0><<<grid, bs, 0, st>>>(h->dc, a);
+  else hessian_kernel<false, 0><<<grid, bs, 0, st>>>(h->dc, a);
   return check_launch();
 }
 

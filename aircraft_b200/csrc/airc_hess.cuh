@@ -50,23 +50,37 @@ struct HessSeed {
   }
 };
 
-// lambda^T Phi(x,u,dt) on jets.  lam[13] in state order.  Returns the jet of the scalar.
-AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c0, float dt, int substeps,
-                                bool normalise, const float lam[13], const HessSeed& seed) {
-  Jet v[3], q[4], w[3];
+// How the p rows are carried through the step: f never reads p, p+ = p + sum over substeps of
+// h/6 (v1 + 2 v2 + 2 v3 + v4), so the Hessian kernel keeps only lambda_p . p+ (one jet), the
+// Jacobian-by-jets kernel the three rows.
+struct PContract {
+  float l[3];
+  Jet acc, tot;
+  AIRC_HD void begin() { acc = jconst(0.0f); }
+  AIRC_HD void stage(float wgt, const Jet sv[3]) { acc = jfma(wgt, jfma(l[2], sv[2], jfma(l[1], sv[1], l[0] * sv[0])), acc); }
+  AIRC_HD void end(const Jet& h6) { tot = jmad(h6, acc, tot); }
+};
+struct PRows {
+  Jet acc[3], tot[3];
+  AIRC_HD void begin() { acc[0] = acc[1] = acc[2] = jconst(0.0f); }
+  AIRC_HD void stage(float wgt, const Jet sv[3]) {
 #pragma unroll
-  for (int i = 0; i < 3; ++i) { v[i] = seed(x0.v[i], i); w[i] = seed(x0.w[i], 7 + i); }
+    for (int i = 0; i < 3; ++i) acc[i] = jfma(wgt, sv[i], acc[i]);
+  }
+  AIRC_HD void end(const Jet& h6) {
 #pragma unroll
-  for (int i = 0; i < 4; ++i) q[i] = seed(x0.q[i], 3 + i);
-  CtlJ c{seed(c0.da, 10), seed(c0.de, 11), seed(c0.dr, 12), seed(c0.df, 13)};
-  const float is = 1.0f / (float)substeps;
-  const Jet h = is * seed(dt, 14);
+    for (int i = 0; i < 3; ++i) tot[i] = jmad(h6, acc[i], tot[i]);
+  }
+};
+
+// Phi(x,u,dt) on jets (base.py:408-480): v, q, w in place; the p rows through PA.
+template <int MODEL, class PA>
+AIRC_HD void state_update_jet(const DevConst& P, Jet v[3], Jet q[4], Jet w[3], const CtlJ& c, const Jet& h,
+                              int substeps, bool normalise, PA& pa) {
   const Jet hh = 0.5f * h, h6 = (1.0f / 6.0f) * h;
-  // lambda_p . p+ : p+ = p + sum over substeps of h/6 (v1 + 2 v2 + 2 v3 + v4), never fed back into f
-  Jet Lp = jconst((lam[0] * x0.p[0] + lam[1] * x0.p[1]) + lam[2] * x0.p[2]);
   for (int sub = 0; sub < substeps; ++sub) {
     Jet sv[3], sq[4], sw[3], av[3], aq[4], aw[3];
-    Jet ap = jconst(0.0f);
+    pa.begin();
 #pragma unroll
     for (int i = 0; i < 3; ++i) { sv[i] = v[i]; sw[i] = w[i]; av[i] = jconst(0.0f); aw[i] = jconst(0.0f); }
 #pragma unroll
@@ -75,8 +89,8 @@ AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c
     for (int stage = 0; stage < 4; ++stage) {
       const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
       Jet kv[3], kq[4], kw[3];
-      f_jet(P, sv, sq, sw, c, kv, kq, kw);
-      ap = jfma(wgt, jfma(lam[2], sv[2], jfma(lam[1], sv[1], lam[0] * sv[0])), ap);
+      f_jet<MODEL>(P, sv, sq, sw, c, kv, kq, kw);
+      pa.stage(wgt, sv);
       const Jet cn = (stage == 2) ? h : hh;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
@@ -91,7 +105,7 @@ AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c
         sq[i] = jmad(cn, kq[i], q[i]);
       }
     }
-    Lp = jmad(h6, ap, Lp);
+    pa.end(h6);
 #pragma unroll
     for (int i = 0; i < 3; ++i) { v[i] = jmad(h6, av[i], v[i]); w[i] = jmad(h6, aw[i], w[i]); }
 #pragma unroll
@@ -102,12 +116,55 @@ AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c
 #pragma unroll
     for (int i = 0; i < 4; ++i) q[i] = q[i] * rn;
   }
-  Jet L = Lp;
+}
+
+AIRC_HD void seed_state_jet(const State& x0, const Ctl& c0, float dt, int substeps, const HessSeed& seed,
+                            Jet v[3], Jet q[4], Jet w[3], CtlJ& c, Jet& h) {
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { v[i] = seed(x0.v[i], i); w[i] = seed(x0.w[i], 7 + i); }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) q[i] = seed(x0.q[i], 3 + i);
+  c = CtlJ{seed(c0.da, 10), seed(c0.de, 11), seed(c0.dr, 12), seed(c0.df, 13)};
+  h = (1.0f / (float)substeps) * seed(dt, 14);
+}
+
+// lambda^T Phi(x,u,dt) on jets.  lam[13] in state order.  Returns the jet of the scalar.
+template <int MODEL = 0>
+AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c0, float dt, int substeps,
+                                bool normalise, const float lam[13], const HessSeed& seed) {
+  Jet v[3], q[4], w[3], h;
+  CtlJ c;
+  seed_state_jet(x0, c0, dt, substeps, seed, v, q, w, c, h);
+  PContract pa;
+  pa.l[0] = lam[0]; pa.l[1] = lam[1]; pa.l[2] = lam[2];
+  pa.tot = jconst((lam[0] * x0.p[0] + lam[1] * x0.p[1]) + lam[2] * x0.p[2]);
+  state_update_jet<MODEL>(P, v, q, w, c, h, substeps, normalise, pa);
+  Jet L = pa.tot;
 #pragma unroll
   for (int i = 0; i < 3; ++i) { L = jfma(lam[3 + i], v[i], L); L = jfma(lam[10 + i], w[i], L); }
 #pragma unroll
   for (int i = 0; i < 4; ++i) L = jfma(lam[6 + i], q[i], L);
   return L;
+}
+
+// x+ with two first-order directions (j0, j1) alongside: out[r].v = x+[r], out[r].g = (d/dz_j0, d/dz_j1).
+// The outer / second-order parts of the jets are seeded with zeros and never read, so the compiler drops
+// them: this is plain two-column forward mode written once for every coefficient model.
+template <int MODEL>
+AIRC_HD void state_update_dual(const DevConst& P, const State& x0, const Ctl& c0, float dt, int substeps,
+                               bool normalise, int j0, int j1, Jet out[13]) {
+  Jet v[3], q[4], w[3], h;
+  CtlJ c;
+  const HessSeed seed{-1, j0, j1};
+  seed_state_jet(x0, c0, dt, substeps, seed, v, q, w, c, h);
+  PRows pa;
+#pragma unroll
+  for (int i = 0; i < 3; ++i) pa.tot[i] = jconst(x0.p[i]);
+  state_update_jet<MODEL>(P, v, q, w, c, h, substeps, normalise, pa);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { out[i] = pa.tot[i]; out[3 + i] = v[i]; out[10 + i] = w[i]; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) out[6 + i] = q[i];
 }
 
 #if defined(__CUDACC__)
@@ -122,7 +179,7 @@ struct HessArgs {
   float* value;              // optional [n]: lambda^T Phi
 };
 
-template <bool SOA>
+template <bool SOA, int MODEL = 0>
 __global__ void __launch_bounds__(128)
 hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
   const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -138,7 +195,7 @@ hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
 #pragma unroll
   for (int r = 0; r < 13; ++r) lam[r] = __ldg(a.lam.base + node * a.lam.sb + r * a.lam.sc);
   const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
-  const Jet L = lagrangian_step_jet(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed);
+  const Jet L = lagrangian_step_jet<MODEL>(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed);
   const long long es = SOA ? a.n : 1;
   float* Hn = a.H + (SOA ? node : node * (NZ * NZ));
   const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);
@@ -159,6 +216,74 @@ hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
       }
     }
     if (a.value && seed.i == 0) a.value[node] = L.v;
+  }
+}
+
+// Jacobian by two-column forward mode on jets, for the coefficient models K2's hand-derived tangents do not
+// cover (poly / linear / default).  8 lanes per node, lane l owns directions (2l, 2l+1) of the 15 active
+// ones (v q w | aileron elevator rudder flaps | dt); outputs and layouts exactly as linearize_coop_kernel.
+template <bool SOA, int MODEL>
+__global__ void __launch_bounds__(128)
+linearize_jet_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long node = gt >> 3;
+  if (node >= a.n) return;
+  const int lane = (int)(gt & 7);
+  State s;
+  load_state(a.x, node, s);
+  const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
+  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
+  Jet out[13];
+  state_update_dual<MODEL>(P, s, c, dt, a.substeps, a.normalise != 0, 2 * lane, 2 * lane + 1, out);
+  const long long es = SOA ? a.n : 1;
+  float* const Ab = a.A ? a.A + (SOA ? node : node * 169) : nullptr;
+  float* const Bb = a.Bm ? a.Bm + (SOA ? node : node * 91) : nullptr;
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    const int d = 2 * lane + half;
+    if (d < 10) {
+      if (Ab)
+#pragma unroll
+        for (int r = 0; r < 13; ++r) Ab[(r * 13 + 3 + d) * es] = half ? out[r].g.hi : out[r].g.lo;
+    } else if (d < 14) {
+      const int col = d == 13 ? 6 : d - 10;
+      if (Bb)
+#pragma unroll
+        for (int r = 0; r < 13; ++r) Bb[(r * 7 + col) * es] = half ? out[r].g.hi : out[r].g.lo;
+    } else if (d == 14) {
+      if (a.Dt) {
+        float* o = a.Dt + (SOA ? node : node * 13);
+#pragma unroll
+        for (int r = 0; r < 13; ++r) o[r * es] = out[r].g.lo;
+      }
+    }
+  }
+  if (lane == 7) {   // x+, the defect, and the constant columns dPhi/dp = [I;0], dPhi/d(thrust) = 0
+    State n;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { n.p[i] = out[i].v; n.v[i] = out[3 + i].v; n.w[i] = out[10 + i].v; }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) n.q[i] = out[6 + i].v;
+    if (a.xn.base) store_state(a.xn, node, n);
+    if (a.r.base) {
+      State t;
+      load_state(a.xt, node, t);
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { t.p[i] -= n.p[i]; t.v[i] -= n.v[i]; t.w[i] -= n.w[i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) t.q[i] -= n.q[i];
+      store_state(a.r, node, t);
+    }
+    if (Ab)
+#pragma unroll
+      for (int r = 0; r < 13; ++r)
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc) Ab[(r * 13 + cc) * es] = (r == cc) ? 1.0f : 0.0f;
+    if (Bb)
+#pragma unroll
+      for (int r = 0; r < 13; ++r)
+#pragma unroll
+        for (int cc = 3; cc < 6; ++cc) Bb[(r * 7 + cc) * es] = 0.0f;
   }
 }
 #endif

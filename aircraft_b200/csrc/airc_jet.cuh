@@ -108,8 +108,79 @@ struct CtlJ {
   Jet da, de, dr, df;
 };
 
+// ---- the registry's other coefficient models on jets (the float versions are in airc_alt.cuh)
+// outputs K0..K1-1 of the degree-3 polynomial table at x (sklearn monomial order), without storing the monomials
+template <int K0, int K1>
+AIRC_HD void poly_eval_jet(const float (*W)[NPOLY + 1], const Jet x[4], Jet* out) {
+#pragma unroll
+  for (int k = K0; k < K1; ++k) {
+    Jet a = jconst(W[k][NPOLY]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a = jfma(W[k][i], x[i], a);
+    out[k - K0] = a;
+  }
+  int t2 = 4, t3 = 14;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+#pragma unroll
+    for (int j = i; j < 4; ++j) {
+      const Jet pij = x[i] * x[j];
+#pragma unroll
+      for (int k = K0; k < K1; ++k) out[k - K0] = jfma(W[k][t2], pij, out[k - K0]);
+      ++t2;
+#pragma unroll
+      for (int l = j; l < 4; ++l) {
+        const Jet pijl = pij * x[l];
+#pragma unroll
+        for (int k = K0; k < K1; ++k) out[k - K0] = jfma(W[k][t3], pijl, out[k - K0]);
+        ++t3;
+      }
+    }
+  }
+}
+AIRC_HD Jet poly_alpha_only_jet(const float w[NPOLY + 1], const Jet& a) {
+  return jmad(a, jmad(a, jfma(w[14], a, jconst(w[4])), jconst(w[0])), jconst(w[NPOLY]));
+}
+
+// NetAlt::adjust on jets (coefficient_models.py:41-135); C excludes the rudder term f_jet adds afterwards
+AIRC_HD void alt_coefficients_jet(const DevConst& P, const Jet vb[3], const Jet& qbar, const Jet& alpha,
+                                  const Jet& beta, const Jet w[3], const CtlJ& c, Jet C[6]) {
+  const AltParams& A = alt_params(P);
+  if (P.model == AIRC_MODEL_POLY_) {
+    const Jet xu = vb[0] + P.eps;
+    const Jet a_el = jatan2(jfma(A.arm, w[1], vb[2]), xu);
+    const Jet a_lw = jatan2(jfma(-0.25f * A.span, w[0], vb[2]), xu);
+    const Jet a_rw = jatan2(jfma(0.25f * A.span, w[0], vb[2]), xu);
+    const Jet vr = jfma(-A.arm, w[2], vb[1]);
+    const Jet b_rud = jasin(vr * jrsqrt(jmad(vb[0], vb[0], jmad(vr, vr, vb[2] * vb[2])) + P.eps));
+    const Jet x0[4] = {alpha, beta, c.da, c.de};
+    poly_eval_jet<0, 4>(A.poly, x0, C);
+    C[3] = jfma(0.125f * A.span, poly_alpha_only_jet(A.poly[2], a_rw) - poly_alpha_only_jet(A.poly[2], a_lw), C[3]);
+    const Jet x1[4] = {a_el, beta, c.da, c.de};
+    poly_eval_jet<4, 5>(A.poly, x1, C + 4);
+    const Jet x2[4] = {alpha, b_rud, c.da, c.de};
+    poly_eval_jet<5, 6>(A.poly, x2, C + 5);
+  } else if (P.model == AIRC_MODEL_LINEAR_) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const float* L = A.lin[k];
+      C[k] = jfma(L[0], qbar, jfma(L[1], alpha, jfma(L[2], beta, jfma(L[3], c.da, jfma(L[4], c.de, jconst(L[5]))))));
+    }
+  } else {
+    const float d2r = 0.01745329252f;
+    C[0] = -(0.3f * (alpha * alpha) + 0.02f);
+    C[1] = -0.98f * beta;
+    C[2] = -5.0f * alpha;
+    C[3] = jfma(0.08f * 4.0f * d2r, c.da, -0.05f * w[0]);
+    C[4] = jfma(-1.2f * 5.0f * d2r, c.de, -0.5f * w[1]);
+    C[5] = -0.05f * w[2];
+  }
+  C[5] = jfma(A.k_rudder_model - P.k_rudder, c.dr, C[5]);
+}
+
 // f(x,u) on jets, the same rotation-matrix form as f_eval_net (base.py:385-406); p_dot = v is left
-// to the caller.
+// to the caller.  MODEL 0: the NN surrogate; 1: the table models of airc_alt.cuh.
+template <int MODEL = 0>
 AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet w[3], const CtlJ& c,
                    Jet vdot[3], Jet qdot[4], Jet wdot[3]) {
   const Jet &x = q[0], &y = q[1], &z = q[2], &s = q[3];
@@ -140,21 +211,25 @@ AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet 
   const Jet beta = jasin(vb[1] * invV);                                                 // base.py:234
 
   Jet C[6];
+  if constexpr (MODEL == 0) {
 #pragma unroll
-  for (int k = 0; k < 6; ++k) C[k] = jconst(P.net.c0[k]);
+    for (int k = 0; k < 6; ++k) C[k] = jconst(P.net.c0[k]);
 #pragma unroll 2
-  for (int j = 0; j < NH; ++j) {
-    const HidPair& hp = P.net.hid[j >> 1];
-    const int e = j & 1;
-    Jet h = jconst(hp.a0[e]);
-    h = jfma(hp.Au[0][e], c.da, h);
-    h = jfma(hp.Au[1][e], c.de, h);
-    h = jfma(hp.Ax[0][e], qbar, h);
-    h = jfma(hp.Ax[1][e], alpha, h);
-    h = jfma(hp.Ax[2][e], beta, h);
-    const Jet r = jsigm2(h);
+    for (int j = 0; j < NH; ++j) {
+      const HidPair& hp = P.net.hid[j >> 1];
+      const int e = j & 1;
+      Jet h = jconst(hp.a0[e]);
+      h = jfma(hp.Au[0][e], c.da, h);
+      h = jfma(hp.Au[1][e], c.de, h);
+      h = jfma(hp.Ax[0][e], qbar, h);
+      h = jfma(hp.Ax[1][e], alpha, h);
+      h = jfma(hp.Ax[2][e], beta, h);
+      const Jet r = jsigm2(h);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) C[k] = jfma(P.net.Wo[k][j], r, C[k]);
+      for (int k = 0; k < 6; ++k) C[k] = jfma(P.net.Wo[k][j], r, C[k]);
+    }
+  } else {
+    alt_coefficients_jet(P, vb, qbar, alpha, beta, w, c, C);
   }
   C[5] = jfma(P.k_rudder, c.dr, C[5]);                       // coefficient_models.py:102-103
   if (P.stall_scaling) {                                     // aircraft.py:280-294

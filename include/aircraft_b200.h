@@ -114,9 +114,9 @@ const char* airc_build_info(void);
 int airc_create(const AircParams* params, const AircNNBlob* nn, int device, AircHandle** out);
 
 /* The registry's other coefficient models (src/aircraft/dynamics/coefficient_models.py:32-37), for
- * airc_state_derivative / airc_state_update / airc_rollout / airc_diagnostics (and their _host
- * variants).  The Jacobian, Hessian, defect and sampling-sweep entry points return AIRC_EUNSUPPORTED
- * on such a handle.
+ * every entry point except the sampling sweep (airc_sweep / airc_sweep_host return AIRC_EUNSUPPORTED on
+ * such a handle): the primal ones run the one-node-per-thread kernels, airc_linearize(_dt) / airc_defects /
+ * airc_hessian run forward mode on jets (airc_hess.cuh).
  *   AIRC_MODEL_POLY     PolynomialModel (coefficient_models.py:106-135; the model of main/control/control.py:166,
  *                       main/mhe/mhtt.py:49, main/rl/rl.py:36).  model_params: float[6][35] = per coefficient
  *                       (CX CY CZ Cl Cm Cn) the 34 weights of the degree-3 monomials of (alpha, beta, aileron,

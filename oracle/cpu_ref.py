@@ -184,6 +184,27 @@ class HostEmul:
                                          x, u, float(dt), x.shape[0], substeps, 1 if normalise else 0, out)
         return out
 
+    def model_linearize(self, model, table, x, u, dt, substeps=1, normalise=False):
+        """linearize_jet_kernel's arithmetic for the table models: (x+, A, B, dPhi/ddt)."""
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        n = x.shape[0]
+        xn, A, Bm, Dt = (np.empty((n,) + s, np.float32) for s in ((13,), (13, 13), (13, 7), (13,)))
+        self.lib.emul_model_linearize.argtypes = [_PP, C.c_int, C.c_void_p, _f32, _f32, C.c_float, C.c_int64, C.c_int,
+                                                  C.c_uint32, _f32, _f32, _f32, _f32]
+        self.lib.emul_model_linearize(C.byref(self.params), model, None if table is None else table.ctypes.data, x, u,
+                                      float(dt), n, substeps, 1 if normalise else 0, xn, A, Bm, Dt)
+        return xn, A, Bm, Dt
+
+    def model_hessian(self, model, table, x, u, lam, dt, substeps=1, normalise=False):
+        x, u, lam = (np.ascontiguousarray(a, np.float32) for a in (x, u, lam))
+        n = x.shape[0]
+        H, g, v = np.empty((n, 21, 21), np.float32), np.empty((n, 21), np.float32), np.empty(n, np.float32)
+        self.lib.emul_model_hessian.argtypes = [_PP, C.c_int, C.c_void_p, _f32, _f32, _f32, C.c_float, C.c_int64,
+                                                C.c_int, C.c_uint32, _f32, _f32, _f32]
+        self.lib.emul_model_hessian(C.byref(self.params), model, None if table is None else table.ctypes.data, x, u,
+                                    lam, float(dt), n, substeps, 1 if normalise else 0, H, g, v)
+        return H, g, v
+
     def model_state_derivative(self, model, table, x, u):
         x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
         out = np.empty_like(x)

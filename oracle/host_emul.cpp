@@ -178,6 +178,64 @@ void emul_model_state_derivative(const AircParams* p, int model, const float* mo
   }
 }
 
+// Jacobian by two-column forward mode on jets (linearize_jet_kernel's arithmetic) for the table models:
+// xn[n][13], A[n][13][13], Bm[n][13][7], Dt[n][13]
+void emul_model_linearize(const AircParams* p, int model, const float* model_params, const float* x,
+                          const float* u, float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
+                          float* Bm, float* Dt) {
+  DevConst P;
+  build_devconst_model(*p, model, model_params, P);
+  memset(A, 0, sizeof(float) * 169 * n);
+  memset(Bm, 0, sizeof(float) * 91 * n);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    for (int r = 0; r < 3; ++r) A[(i * 13 + r) * 13 + r] = 1.0f;
+    for (int lane = 0; lane < 8; ++lane) {
+      Jet out[13];
+      state_update_dual<1>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, 2 * lane, 2 * lane + 1, out);
+      for (int half = 0; half < 2; ++half) {
+        const int d = 2 * lane + half;
+        for (int r = 0; r < 13; ++r) {
+          const float val = half ? out[r].g.hi : out[r].g.lo;
+          if (d < 10) A[(i * 13 + r) * 13 + 3 + d] = val;
+          else if (d < 14) Bm[(i * 13 + r) * 7 + (d == 13 ? 6 : d - 10)] = val;
+          else if (d == 14) Dt[i * 13 + r] = val;
+        }
+      }
+      if (lane == 7) for (int r = 0; r < 13; ++r) xn[13 * i + r] = out[r].v;
+    }
+  }
+}
+
+void emul_model_hessian(const AircParams* p, int model, const float* model_params, const float* x, const float* u,
+                        const float* lam, float dt, int64_t n, int substeps, uint32_t flags, float* H, float* grad,
+                        float* value) {
+  DevConst P;
+  build_devconst_model(*p, model, model_params, P);
+  memset(H, 0, sizeof(float) * NZ * NZ * n);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* Hn = H + i * NZ * NZ;
+    float* g = grad + i * NZ;
+    for (int r = 0; r < 3; ++r) { g[r] = lam[13 * i + r]; g[16 + r] = 0.f; }
+    for (int t = 0; t < HESS_LANES; ++t) {
+      HessSeed seed;
+      hess_task(t, seed.i, seed.j0, seed.j1);
+      const Jet L = lagrangian_step_jet<1>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE, lam + 13 * i, seed);
+      const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);
+      Hn[zi * NZ + z0] = Hn[z0 * NZ + zi] = L.og.lo;
+      if (seed.j1 < NHACT) {
+        const int z1 = hess_zindex(seed.j1);
+        Hn[zi * NZ + z1] = Hn[z1 * NZ + zi] = L.og.hi;
+      }
+      if (seed.j0 == seed.i) g[zi] = L.o;
+      if (t == 0) value[i] = L.v;
+    }
+  }
+}
+
 // K3 arithmetic (airc_hess.cuh): the 64 (outer, inner-pair) tasks of a node, one after the other.
 // H[n][21][21] (zero-filled here), grad[n][21], value[n]
 void emul_hessian(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,

@@ -52,3 +52,29 @@ def test_poly_reproduces_reference_stored_trajectory(built, golden_dir):
     mid, tab = _tables(golden_dir)["poly"]
     got = emu.model_state_update(mid, tab, X[:-1], U[:-1], 0.1, 10, False)
     assert col_err(got, X[1:]) < PARITY_TOL
+
+
+@pytest.mark.parametrize("model", ["poly", "linear", "default"])
+def test_model_derivatives_vs_oracle(built, golden_dir, model):
+    """A, B, dPhi/ddt by two-column forward mode on jets and the Lagrangian Hessian by second-order jets for
+    the table models (what IPOPT derives for the reference's 'poly' MPC), against jacfwd of the float64 oracle."""
+    p, blob = params_for(TRIM)
+    emu, orc = HostEmul(p, blob), oracle_for(TRIM, coeff_model=model)
+    mid, tab = _tables(golden_dir)[model]
+    n = 96
+    x, u = make_states(n, seed=74, perturb_norm=1e-3), make_controls(n, seed=74)
+    x[:, 10:13] *= 3.0
+    lam = np.random.default_rng(74).normal(size=(n, 13)).astype(np.float32)
+    for ns, nm in [(1, False), (2, True)]:
+        xn, A, B, Dt = emu.model_linearize(mid, tab, x, u, 0.01, ns, nm)
+        xo, Ao, Bo, Do = orc.linearize(t64(x), t64(u), 0.01, ns, nm, want_dt=True)
+        assert col_err(xn, xo.numpy()) < PARITY_TOL
+        assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+        assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+        assert col_err(Dt, Do.numpy(), atol=1e-3) < PARITY_TOL
+    H, g, v = emu.model_hessian(mid, tab, x, u, lam, 0.01, 1, True)
+    Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.01, 1, True))
+    # second-order entries: 5e-5 of each entry's own scale over the batch (FP32 cancellation in the
+    # q-bar-linear terms of the 'linear' table reaches 1.3e-5; 'poly' and 'default' stay below 1e-5)
+    assert col_err(H, Ho, atol=1e-3) < 5e-5 and col_err(g, go) < PARITY_TOL
+    assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
