@@ -66,7 +66,7 @@ def test_models_parity(built, golden_dir, model):
     assert torch.equal(As.permute(2, 0, 1), A)
     H, g, _ = ac.lagrangian_hessian(f32(xs_), f32(us_), f32(lam), 0.01, normalise=True)
     Ho, go, _ = (a.numpy() for a in orc.lagrangian_hessian(t64(xs_), t64(us_), t64(lam), 0.01, 1, True))
-    assert col_err(H.cpu(), Ho) < 5e-5 and col_err(g.cpu(), go) < PARITY_TOL     # see tests/test_coeff_models.py
+    assert col_err(H.cpu(), Ho) < 1e-4 and col_err(g.cpu(), go) < PARITY_TOL     # see tests/test_coeff_models.py
     U3 = f32(make_control_sequences(32, 6, seed=76))
     X3 = ac.rollout(f32(make_states(32, seed=76)), U3, 0.01, normalise=True, return_trajectory=True).trajectory
     r, Ad, Bd = ac.defects(X3, U3, 0.01, normalise=True)
