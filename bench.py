@@ -619,6 +619,34 @@ def side_measurements(torch, ac, dev, rank, args):
         except Exception as e:  # the checker is optional for this side line
             out["c1"]["cpu_baseline"] = {"unavailable": repr(e)}
 
+    # The reference's only published timings (todo.md:38): IPOPT callbacks at 298 nodes with the
+    # analytic DEFAULT coefficient model on one CPU thread.  The same numeric blocks on the GPU, same model.
+    try:
+        from aircraft_b200 import Aircraft
+        from aircraft_b200.config import TRIM_COM
+        acd = Aircraft.from_problem(com=TRIM_COM, device=dev.index, coeff_model_type="default",
+                                    physical_integration_substeps=1, normalise=True)
+        nn_ = 298
+        xa = torch.tensor(make_states(nn_, seed=700 + rank), dtype=torch.float32, device=dev)
+        ua = torch.tensor(make_controls(nn_, seed=700 + rank), dtype=torch.float32, device=dev)
+        la = torch.randn(nn_, 13, device=dev, generator=torch.Generator(device=dev).manual_seed(700 + rank))
+        xt = acd.state_update(xa.T.contiguous(), ua.T.contiguous(), DT).T.contiguous()
+        Xw = torch.cat([xa[:1], xt], 0)[None]                    # a [1, 299, 13] guess, U [1, 298, 7]
+        t_g = time_launches(torch, lambda: acd.state_update(xa.T, ua.T, DT), max(K, 20), 3, flush)
+        t_j = time_launches(torch, lambda: acd.defects(Xw, ua[None], DT), max(K, 20), 3, flush)
+        t_h = time_launches(torch, lambda: acd.lagrangian_hessian(xa, ua, la, DT), max(K, 20), 3, flush)
+        out["mpc_blocks_default_298"] = {
+            "workload": "298 shooting nodes, DEFAULT coefficient model, 1 substep: the dynamics blocks behind IPOPT's "
+                        "nlp_g / nlp_jac_g / nlp_hess_l callbacks (values, defect Jacobian blocks A B, exact Hessian blocks)",
+            "unit": "ms per evaluation", "higher_is_better": False,
+            "state_update_ms": t_g, "defects_with_jacobian_blocks_ms": t_j, "lagrangian_hessian_ms": t_h,
+            "reference_published": {"nlp_g_ms": 0.65752, "nlp_jac_g_ms": 14.24, "nlp_hess_l_ms": 55.79,
+                                    "source": "reference todo.md:38 via BASELINE.md section 2 (unknown CPU, 1 thread; whole-NLP "
+                                              "callbacks incl. non-dynamics constraints: context, not a like-for-like ratio)"},
+            "l2": "flushed between launches"}
+    except Exception as e:   # side line only
+        out["mpc_blocks_default_298"] = {"unavailable": repr(e)}
+
     # row f.1: exact Lagrangian-Hessian blocks at the reference's horizon (298 nodes, todo.md tables) and in bulk
     for name, nh in (("hessian_298", 298), ("hessian_bulk", 262_144)):
         x = torch.tensor(make_states(nh, seed=600 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev).contiguous()
