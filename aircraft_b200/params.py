@@ -168,7 +168,11 @@ def load_poly_model(path, rudder_moment_arm: float = 0.5) -> np.ndarray:
 def load_linear_model(path) -> np.ndarray:
     """float32[36] for AIRC_MODEL_LINEAR: the six rows of data/networks/linearised.csv
     (q, alpha, beta, aileron, elevator, intercept), as LinearModel reads them (coefficient_models.py:80-84)."""
-    a = np.loadtxt(path, delimiter=",", skiprows=1, dtype=np.float64)
+    path = Path(path)
+    if path.suffix == ".npz":      # tests/golden/make_poly_golden.py
+        a = np.asarray(np.load(path)["table"], np.float64)
+    else:
+        a = np.loadtxt(path, delimiter=",", skiprows=1, dtype=np.float64)
     if a.shape != (6, 6):
         raise RuntimeError(f"{path}: expected a 6x6 coefficient table, got {a.shape}")
     return a.astype(np.float32).reshape(-1)

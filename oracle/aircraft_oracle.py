@@ -126,7 +126,7 @@ class OracleConfig:
     stall_scaling: bool = False        # aircraft.py:30
     coeff_model: str = "nn"            # 'nn' | 'default' (fixture) | 'poly' (fixture: pins Phi on the reference's stored trajectory)
     rudder_moment_arm: float = 0.5     # utils.py:215 (AircraftConfiguration default; absent from the JSON)
-    linear_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "linearised.csv")
+    linear_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "linear_model.npz")
     poly_path: Path | str = field(default=Path(__file__).resolve().parent.parent / "tests" / "golden" / "poly_model.npz")
     legacy_thrust: bool = False        # todo.md era: forces += thrust (now commented, aircraft.py:320)
     weights: Path | str = field(default=DEFAULT_WEIGHTS)
@@ -156,9 +156,9 @@ class AircraftOracle:
         self.com = torch.tensor([x, y, z], dtype=F64)
         self.g = torch.tensor(list(c.gravity), dtype=F64)
         self.nn = SurrogateF64(c.weights) if c.coeff_model == "nn" else None
-        if c.coeff_model == "linear":  # the six rows of data/networks/linearised.csv (copied to tests/golden/)
+        if c.coeff_model == "linear":  # the six rows of data/networks/linearised.csv (tests/golden/make_poly_golden.py)
             import numpy as _np
-            self.lin = torch.tensor(_np.loadtxt(c.linear_path, delimiter=",", skiprows=1), dtype=F64)
+            self.lin = torch.tensor(_np.load(c.linear_path)["table"], dtype=F64)
         if c.coeff_model == "poly":   # tests/golden/make_poly_golden.py
             import numpy as _np
             d = _np.load(c.poly_path)

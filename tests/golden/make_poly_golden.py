@@ -50,6 +50,11 @@ def main():
     intercept = np.array([float(fm[k]["intercept"]) for k in names])
     np.savez(OUT, powers=powers, coef=coef, intercept=intercept, features=np.array(["alpha", "beta", "aileron", "elevator"]))
     print("wrote", OUT, powers.shape, coef.shape)
+    # the linear model's 6x6 table (q, alpha, beta, aileron, elevator, intercept), LinearModel coefficient_models.py:80-84
+    lin = np.loadtxt("/root/reference/data/networks/linearised.csv", delimiter=",", skiprows=1)
+    assert lin.shape == (6, 6)
+    np.savez(OUT.parent / "linear_model.npz", table=lin, columns=np.array(["q", "alpha", "beta", "aileron", "elevator", "intercept"]))
+    print("wrote", OUT.parent / "linear_model.npz")
 
 
 if __name__ == "__main__":

@@ -91,7 +91,7 @@ def test_facade_mirrors_reference_interface(built):
     gold = ROOT / "tests" / "golden"
     pm = Aircraft(AircraftOpts(coeff_model_type="poly", coeff_model_path=gold / "poly_model.npz", aircraft_config=cfg))
     assert pm.coefficient_model.table.shape == (211,) and pm.coefficient_model.model_id == 1
-    lm = Aircraft(AircraftOpts(coeff_model_type="linear", coeff_model_path=gold / "linearised.csv", aircraft_config=cfg))
+    lm = Aircraft(AircraftOpts(coeff_model_type="linear", coeff_model_path=gold / "linear_model.npz", aircraft_config=cfg))
     assert lm.coefficient_model.table.shape == (36,)
     assert Aircraft(AircraftOpts(coeff_model_type="default", aircraft_config=cfg)).coefficient_model.table is None
     with pytest.raises(RuntimeError):

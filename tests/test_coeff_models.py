@@ -16,7 +16,7 @@ TRIM = (0.0131991, -1.78875e-08, 0.00313384)
 
 def _tables(golden_dir):
     return {"poly": (MODEL_POLY, load_poly_model(golden_dir / "poly_model.npz")),
-            "linear": (MODEL_LINEAR, load_linear_model(golden_dir / "linearised.csv")),
+            "linear": (MODEL_LINEAR, load_linear_model(golden_dir / "linear_model.npz")),
             "default": (MODEL_DEFAULT, None)}
 
 

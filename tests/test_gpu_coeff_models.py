@@ -19,7 +19,7 @@ def f32(a):
 
 def _aircraft(model, golden_dir, **kw):
     from aircraft_b200 import Aircraft
-    path = {"poly": golden_dir / "poly_model.npz", "linear": golden_dir / "linearised.csv", "default": ""}[model]
+    path = {"poly": golden_dir / "poly_model.npz", "linear": golden_dir / "linear_model.npz", "default": ""}[model]
     return Aircraft.from_problem(com=TRIM, device=DEV, coeff_model_type=model, coeff_model_path=path, **kw)
 
 
