@@ -348,12 +348,13 @@ def fp32_peak(ac):
 
 def ncu_traffic(kernel: str):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
-    capture of this workload (profiles/r1f_ncu_summary_sweep2.txt); None when the summary is not there."""
+    capture of this workload (profiles/r*_ncu_summary_sweep2.txt, latest); None when the summary is not there."""
     unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
     try:
         rd = wr = None
         hit = False
-        for ln in (ROOT / "profiles" / "r1f_ncu_summary_sweep2.txt").read_text().splitlines():
+        cands = sorted((ROOT / "profiles").glob("r*_ncu_summary_sweep2.txt"))      # the latest committed capture
+        for ln in cands[-1].read_text().splitlines():
             t = ln.split()
             if ln.startswith("Kernel Name"):
                 hit = kernel in ln
