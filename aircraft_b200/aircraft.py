@@ -59,8 +59,8 @@ class NeuralModel(CoefficientModel):
 
 class _TableModel(CoefficientModel):
     """The registry's other models (coefficient_models.py:41-135) as parameter tables for
-    airc_create_model.  Everything but the sampling sweep is served: the primal entry points by the
-    one-node-per-thread kernels, linearize / defects / lagrangian_hessian by forward mode on jets."""
+    airc_create_model.  Every entry point is served: the primal ones and the sampling sweep by the
+    one-node / one-trajectory-per-thread kernels, linearize / defects / lagrangian_hessian by forward mode on jets."""
     blob = None
     model_id = 0
 

@@ -437,7 +437,6 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
   if (!h || !x0 || (!U_nom && H > 0) || !sp || !cp || !record || B < 0 || B > 0xFFFFFFFFLL || H < 0 ||
       substeps < 1 || (flags & ~(uint32_t)AIRC_FLAG_NORMALISE))
     return fail(AIRC_EINVAL, "airc_sweep: bad argument%s", "");
-  if (h->dc.model) return fail(AIRC_EUNSUPPORTED, "airc_sweep: the sampling sweep is built for the 'nn' coefficient model only%s", "");
   const int C = ckpt_interval_of(H, sp->ckpt_interval);
   const int S = H > 0 ? (H + C - 1) / C : 1;
   const size_t need_min = 256;
@@ -508,8 +507,11 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
     a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
     const int bs = (B <= (int64_t)h->sm_count * 32 * 2) ? 32 : ((B <= (int64_t)h->sm_count * 64 * 4) ? 64 : AIRC_ROLLOUT_BS);
     const unsigned grid = (unsigned)((B + bs - 1) / bs);
-    if (use_ckpt) sweep_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
-    else sweep_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+    if (h->dc.model) {
+      if (use_ckpt) sweep_kernel<true, 1><<<grid, bs, 0, st>>>(h->dc, a);
+      else sweep_kernel<false, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    } else if (use_ckpt) sweep_kernel<true, 0><<<grid, bs, 0, st>>>(h->dc, a);
+    else sweep_kernel<false, 0><<<grid, bs, 0, st>>>(h->dc, a);
   }
   WinnerArgs w;
   memset(&w, 0, sizeof(w));
@@ -517,7 +519,8 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
   w.B = B; w.H = H; w.C = use_ckpt ? C : (H > 0 ? H : 1); w.substeps = substeps;
   w.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
   const int wthreads = use_ckpt ? S : 1;
-  sweep_winner_kernel<<<(wthreads + 31) / 32, 32, 0, st>>>(h->dc, w);
+  if (h->dc.model) sweep_winner_kernel<1><<<(wthreads + 31) / 32, 32, 0, st>>>(h->dc, w);
+  else sweep_winner_kernel<0><<<(wthreads + 31) / 32, 32, 0, st>>>(h->dc, w);
   return check_launch();
 }
 

@@ -58,7 +58,7 @@ AIRC_D void load_state_uniform(const float* x, State& s) {
   for (int i = 0; i < 4; ++i) s.q[i] = __ldg(x + 6 + i);
 }
 
-template <bool CKPT>
+template <bool CKPT, int MODEL = 0>
 __global__ void __launch_bounds__(AIRC_ROLLOUT_BS, AIRC_ROLLOUT_MINBLOCKS)
 sweep_kernel(const __grid_constant__ DevConst P, const SweepArgs a) {
   const long long braw = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -98,7 +98,7 @@ sweep_kernel(const __grid_constant__ DevConst P, const SweepArgs a) {
     for (int c = 0; c < 4; ++c) up[c] = un[c];
     sum_v2 += body_speed2(P, s);
     const Ctl c{un[0], un[1], un[2], un[3]};
-    state_update<0>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
+    state_update<0, MODEL>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
   }
   const float ex = s.p[0] - a.cc.goal0, ey = s.p[1] - a.cc.goal1, ez = s.p[2] - z0;
   float J = a.cc.w_goal * (ex * ex + ey * ey);
@@ -134,6 +134,7 @@ struct WinnerArgs {
 
 // Thread j owns steps [j*C, min(H,(j+1)*C)): it starts from checkpoint j (x0 for j = 0) and
 // repeats the sweep kernel's arithmetic, so the record is the trajectory the cost was computed on.
+template <int MODEL = 0>
 __global__ void sweep_winner_kernel(const __grid_constant__ DevConst P, const WinnerArgs a) {
   const unsigned long long key = *a.key;
   const long long b = (long long)(key & 0xFFFFFFFFull);
@@ -174,7 +175,7 @@ __global__ void sweep_winner_kernel(const __grid_constant__ DevConst P, const Wi
 #pragma unroll
     for (int c = 3; c < 6; ++c) uo[c] = a.Unom[k * 7 + c];
     const Ctl c{un[0], un[1], un[2], un[3]};
-    state_update<0>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
+    state_update<0, MODEL>(P, s, c, a.dt, a.substeps, a.normalise != 0, nullptr);
     const VecViewW tk{traj + 13 * (k + 1), 0, 1};
     store_state(tk, 0, s);
   }

@@ -43,7 +43,7 @@ extern "C" {
 #define AIRC_ECUDA (-2)    /* CUDA runtime error; text via airc_last_error() */
 #define AIRC_ENODEV (-3)   /* no usable sm_100 device */
 #define AIRC_ENOMEM (-4)
-#define AIRC_EUNSUPPORTED (-5) /* entry point not built for this handle's coefficient model */
+#define AIRC_EUNSUPPORTED (-5) /* reserved: entry point not built for this handle's coefficient model (none today) */
 
 /* layout of batched vectors */
 #define AIRC_LAYOUT_SOA 0  /* [13][B] / [H][7][B]: batch index fastest -- the native layout; it is
@@ -114,9 +114,9 @@ const char* airc_build_info(void);
 int airc_create(const AircParams* params, const AircNNBlob* nn, int device, AircHandle** out);
 
 /* The registry's other coefficient models (src/aircraft/dynamics/coefficient_models.py:32-37), for
- * every entry point except the sampling sweep (airc_sweep / airc_sweep_host return AIRC_EUNSUPPORTED on
- * such a handle): the primal ones run the one-node-per-thread kernels, airc_linearize(_dt) / airc_defects /
- * airc_hessian run forward mode on jets (airc_hess.cuh).
+ * every entry point: the primal ones and the sampling sweep run the one-node / one-trajectory-per-thread
+ * kernels (the packed two-trajectory kernels are NN-only), airc_linearize(_dt) / airc_defects / airc_hessian
+ * run forward mode on jets (airc_hess.cuh).
  *   AIRC_MODEL_POLY     PolynomialModel (coefficient_models.py:106-135; the model of main/control/control.py:166,
  *                       main/mhe/mhtt.py:49, main/rl/rl.py:36).  model_params: float[6][35] = per coefficient
  *                       (CX CY CZ Cl Cm Cn) the 34 weights of the degree-3 monomials of (alpha, beta, aileron,

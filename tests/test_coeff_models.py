@@ -79,3 +79,17 @@ def test_model_derivatives_vs_oracle(built, golden_dir, model):
     # d2/d(q_z)d(aileron) ~ 3e-2 against d2/ddt2 ~ 1e6) carry FP32 cancellation noise of 1e-5 .. 6e-5
     assert col_err(H, Ho, atol=1e-3) < 1e-4 and col_err(g, go) < PARITY_TOL
     assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
+
+
+REF_PICKLE = "/root/reference/data/networks/fitted_models_casadi.pkl"
+
+
+@pytest.mark.skipif(not __import__("os").path.exists(REF_PICKLE), reason="the reference tree is only present in the build container")
+def test_poly_table_read_from_the_reference_pickle_without_casadi(golden_dir):
+    """The facade's 'poly' loader on the reference's own pickle (CasADi and sklearn classes stubbed out while
+    unpickling) gives the same table as the committed fixture."""
+    a = load_poly_model(REF_PICKLE, rudder_moment_arm=0.5)
+    b = load_poly_model(golden_dir / "poly_model.npz", rudder_moment_arm=0.5)
+    assert np.array_equal(a, b)
+    lin = load_linear_model("/root/reference/data/networks/linearised.csv")
+    assert np.array_equal(lin, load_linear_model(golden_dir / "linear_model.npz"))

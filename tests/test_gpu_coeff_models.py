@@ -73,9 +73,22 @@ def test_models_parity(built, golden_dir, model):
     fin = torch.isfinite(X3).all(-1).all(-1) & (X3[:, :, 10:13].abs().amax((1, 2)) < 20.0)   # still in the envelope
     assert fin.sum() >= 8
     assert float(r[fin].abs().max()) < 2e-5 * float(X3[fin].abs().max())
-    # the sampling sweep stays NN-only and says so
-    with pytest.raises(RuntimeError, match="nn"):
-        ac.sweep(f32(xs_[0]), f32(np.zeros((10, 7))), 0.01, 64)
+    # the sampling sweep (one-trajectory kernels for these models) against explicit rollouts of the same controls
+    from aircraft_b200.params import make_cost_params, make_sweep_params
+    Bs, Hs = 700, 12
+    x0s = make_states(1, seed=77, level=True)[0]
+    Un = np.zeros((Hs, 7), np.float32); Un[:, 1] = -0.5
+    sp, cp = make_sweep_params(seed=9), make_cost_params()
+    wsw = ac.sweep(f32(x0s), f32(Un), 0.01, Bs, sampler=sp, cost=cp, normalise=True, return_costs=True)
+    Us = ac.sweep_controls(f32(Un), sp, 0, Bs)
+    rr = ac.rollout(f32(np.repeat(x0s[None], Bs, 0)), Us, 0.01, normalise=True, cost=cp, return_trajectory=True)
+    okc = torch.isfinite(rr.cost)
+    assert okc.sum() > Bs // 2
+    assert col_err(wsw.cost[okc].cpu()[:, None], rr.cost[okc].cpu().numpy()[:, None]) < PARITY_TOL
+    j = int(wsw.argmin)
+    assert j == int(torch.argmin(torch.nan_to_num(rr.cost, nan=float("inf"))))
+    assert col_err(wsw.trajectory.cpu(), rr.trajectory[j].cpu().numpy()) < 5e-5
+    assert torch.equal(wsw.controls, Us[j])
 
 
 def test_poly_kernels_reproduce_reference_stored_trajectory(built, golden_dir):
