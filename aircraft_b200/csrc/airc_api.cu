@@ -21,6 +21,7 @@ struct AircHandle {
   DevConst dc;
   UnitNet un;          // the surrogate in unit-major order for the packed (two-trajectory) kernels
   int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0 / 2: force scalar / packed
+  int coop = 0;        // AIRC_ROLLOUT_COOP=1|2|4|8: small-batch rollouts on the lanes-per-trajectory kernel without the flag
   int device;
   int sm_count;
   // used only by the *_host entry points (those are not re-entrant per handle)
@@ -100,6 +101,10 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   build_devconst(*params, *nn, h->dc);
   make_unit_net(h->dc.net, h->un);
   if (const char* e = getenv("AIRC_ROLLOUT_IMPL")) h->packed = atoi(e) == 1 ? 0 : 2;   // 0 scalar only, 1 auto, 2 packed always
+  if (const char* e = getenv("AIRC_ROLLOUT_COOP")) {   // 0 off, 1 auto, 2/4/8 force that many lanes (A/B timing)
+    const int v = atoi(e);
+    h->coop = (v == 0 || v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
+  }
   h->device = device;
   h->sm_count = prop.multiProcessorCount;
   *out = h;
@@ -191,7 +196,7 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
                  int H, int substeps, uint32_t flags, int layout, float* X, float* x_final,
                  float* cost, const AircCostParams* cp, void* stream) {
   if (!h || B < 0 || H < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
-      (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U)) || (cost && !cp))
+      (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U | AIRC_FLAG_COOPERATIVE)) || (cost && !cp))
     return fail(AIRC_EINVAL, "airc_rollout: bad argument%s", "");
   if (B == 0) return AIRC_OK;   // empty batch: nothing to read, so NULL data pointers are fine
   if (!x0 || (!U && H > 0)) return fail(AIRC_EINVAL, "airc_rollout: NULL x0 or U%s", "");
@@ -230,6 +235,25 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
     else if (cost) rollout_kernel<true, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
     else if (X) rollout_kernel<false, true, 1><<<grid, bs, 0, st>>>(h->dc, a);
     else rollout_kernel<false, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
+    return check_launch();
+  }
+  // small batches (latency case, config 2), opt-in by AIRC_FLAG_COOPERATIVE: 8 / 4 / 2 lanes per trajectory while
+  // the batch still fits one warp per sub-partition.
+  if (h->packed == 1 && (h->coop || (flags & AIRC_FLAG_COOPERATIVE)) && B * 2 <= (long long)h->sm_count * 128) {
+    const long long slots = (long long)h->sm_count * 128;          // threads of one warp per sub-partition
+    const int L = h->coop > 1 ? h->coop : (B * 8 <= slots ? 8 : (B * 4 <= slots ? 4 : 2));
+    const unsigned gridc = (unsigned)((B * L + 127) / 128);
+#define AIRC_COOP_LAUNCH(LL)                                                                             \
+    do {                                                                                                 \
+      if (cost && X) rollout_coop_kernel<true, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);              \
+      else if (cost) rollout_coop_kernel<true, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);             \
+      else if (X) rollout_coop_kernel<false, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);                \
+      else rollout_coop_kernel<false, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);                      \
+    } while (0)
+    if (L == 8) AIRC_COOP_LAUNCH(8);
+    else if (L == 4) AIRC_COOP_LAUNCH(4);
+    else AIRC_COOP_LAUNCH(2);
+#undef AIRC_COOP_LAUNCH
     return check_launch();
   }
   if (h->packed == 2 || (h->packed == 1 && B >= 2 * wave2)) {

@@ -39,8 +39,60 @@ struct NetCoop {
   const FusedNet* net;   // shared-memory copy when L > 1 (lane-dependent addresses)
   int lane;              // 0..L-1 within the node group
 
+  // Primal only.  The six sums are formed in ONE association whatever L is: eight "virtual lanes" v, each
+  // accumulating the pairs (v, v+8), combined by the xor butterfly 4, 2, 1 -- the steps with offset >= L happen
+  // inside the thread, the rest by shuffles.  The small-batch rollout kernel picks L by batch size, so this keeps
+  // a sharded batch bit-identical to the whole one.
+  AIRC_HD void eval_primal(float qbar, float alpha, float beta, const Ctl& c, float C[6]) const {
+    constexpr int V = 8, NV = V / L;
+    const F2 da = bc2(c.da), de = bc2(c.de), qb = bc2(qbar), al = bc2(alpha), be = bc2(beta);
+    F2 part[NV][3];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int vl = lane + j * L;
+      F2 acc[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) acc[k] = F2{0.0f, 0.0f};
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int p = vl + m * V;
+        const HidPair& w = net->hid[p];
+        F2 h = F2{w.a0[0], w.a0[1]};
+        h = fma2(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+        h = fma2(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+        h = fma2(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+        h = fma2(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+        h = fma2(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+        const F2 r = sigm2_x2(h);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) acc[k] = fma2(F2{net->Wo[k][2 * p], net->Wo[k][2 * p + 1]}, r, acc[k]);
+      }
+#pragma unroll
+      for (int kk = 0; kk < 3; ++kk)
+        part[j][kk] = F2{acc[2 * kk].lo + acc[2 * kk].hi, acc[2 * kk + 1].lo + acc[2 * kk + 1].hi};
+    }
+#pragma unroll
+    for (int off = V / 2; off >= L; off >>= 1) {
+      const int st = off / L;
+#pragma unroll
+      for (int j = 0; j < st; ++j)
+#pragma unroll
+        for (int kk = 0; kk < 3; ++kk) part[j][kk] = add2(part[j][kk], part[j + st][kk]);
+    }
+#pragma unroll
+    for (int kk = 0; kk < 3; ++kk) {
+      const F2 a = group_sum2<L>(part[0][kk]);
+      C[2 * kk] = a.lo + net->c0[2 * kk];
+      C[2 * kk + 1] = a.hi + net->c0[2 * kk + 1];
+    }
+  }
+
   template <bool WITH_JAC>
   AIRC_HD void eval(float qbar, float alpha, float beta, const Ctl& c, float C[6], float J[6][5]) const {
+    if constexpr (!WITH_JAC) {
+      eval_primal(qbar, alpha, beta, c, C);
+      return;
+    }
     F2 acc[6], Jacc[6][5];
 #pragma unroll
     for (int k = 0; k < 6; ++k) {
@@ -87,6 +139,56 @@ struct NetCoop {
   }
   AIRC_HD void adjust(const DevConst&, Stage&, const float*, const Ctl&) const {}
 };
+
+// Primal RK4 step with the network evaluated through a policy (NetCoop: shared by the lanes of a group).
+// Same arithmetic as rk4_step<0> apart from the network's summation order.
+template <class Net>
+AIRC_HD void rk4_step_net(const DevConst& P, const Net& net, State& x, const Ctl& c, float h) {
+  const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
+  float sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) { sv[i] = x.v[i]; sw[i] = x.w[i]; ap[i] = av[i] = aw[i] = 0.0f; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { sq[i] = x.q[i]; aq[i] = 0.0f; }
+#pragma unroll 1
+  for (int stage = 0; stage < 4; ++stage) {
+    const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
+    const float cn = (stage == 2) ? h : hh;
+    float kv[3], kq[4], kw[3];
+    Stage st;
+    float J[6][5];
+    f_eval_net<false>(P, net, sv, sq, sw, c, kv, kq, kw, st, J);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      ap[i] = fmaf(wgt, sv[i], ap[i]);
+      av[i] = fmaf(wgt, kv[i], av[i]);
+      aw[i] = fmaf(wgt, kw[i], aw[i]);
+      sv[i] = fmaf(cn, kv[i], x.v[i]);
+      sw[i] = fmaf(cn, kw[i], x.w[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      aq[i] = fmaf(wgt, kq[i], aq[i]);
+      sq[i] = fmaf(cn, kq[i], x.q[i]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    x.p[i] = fmaf(h6, ap[i], x.p[i]);
+    x.v[i] = fmaf(h6, av[i], x.v[i]);
+    x.w[i] = fmaf(h6, aw[i], x.w[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) x.q[i] = fmaf(h6, aq[i], x.q[i]);
+}
+
+template <class Net>
+AIRC_HD void state_update_net(const DevConst& P, const Net& net, State& x, const Ctl& c, float dt, int substeps,
+                              bool normalise) {
+  const float h = (substeps == 1) ? dt : dt / (float)substeps;
+  for (int s = 0; s < substeps; ++s) rk4_step_net(P, net, x, c, h);
+  if (normalise) normalise_q<0>(x, nullptr);
+}
 
 template <class T>
 struct TangentT {

@@ -248,6 +248,74 @@ rollout_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------ K1 (small batches)
+// Latency case (BASELINE config 2: 4096 trajectories leave three quarters of the sub-partitions idle with one
+// trajectory per thread): L = 8, 4 or 2 lanes share one trajectory, chosen so that the batch still runs as one
+// warp per sub-partition.  Each lane evaluates 16/L of the hidden-unit pairs, the six coefficient sums are
+// all-reduced by xor-shuffles (NetCoop), the rest of f is replicated (it is the latency chain, not the
+// throughput, that matters here).  Lane 0 stores.
+template <bool COST, bool TRAJ, int L>
+__global__ void __launch_bounds__(128)
+rollout_coop_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
+  __shared__ FusedNet snet;
+  {
+    const float* src = reinterpret_cast<const float*>(&P.net);
+    float* dst = reinterpret_cast<float*>(&snet);
+    for (int i = threadIdx.x; i < (int)(sizeof(FusedNet) / sizeof(float)); i += blockDim.x) dst[i] = src[i];
+  }
+  __syncthreads();
+  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long braw = gt / L;
+  const int lane = (int)(gt % L);
+  const bool live = braw < a.B;
+  const long long b = live ? braw : a.B - 1;          // whole warps stay alive for the shuffles
+  const bool writer = live && lane == 0;
+  State s;
+  load_state(a.x0, b, s);
+  const float z0 = s.p[2];
+  const float* u = a.U + b * a.u_sb;
+  float* Xb = TRAJ ? a.X + b * a.X_sb : nullptr;
+  if (TRAJ && writer) store_state(VecViewW{Xb, 0, a.X_sc}, 0, s);
+  const NetCoop<L> net{&snet, lane};
+  float sum_du = 0.0f, sum_v2 = 0.0f;
+  float up[7];
+#pragma unroll 1
+  for (int k = 0; k < a.H; ++k) {
+    const float* uk = u + k * a.u_sk;
+    const Ctl c = load_ctl(uk, a.u_sc);
+    if (COST) {
+      float un[7];
+      un[0] = c.da; un[1] = c.de; un[2] = c.dr; un[6] = c.df;
+#pragma unroll
+      for (int i = 3; i < 6; ++i) un[i] = __ldg(uk + i * a.u_sc);
+      if (k > 0) {
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+          const float d = un[i] - up[i];
+          sum_du += 1.0f - fast_ex2(d * d * a.cc.neg_log2e_over_eps);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 7; ++i) up[i] = un[i];
+      sum_v2 += body_speed2(P, s);
+    }
+    state_update_net(P, net, s, c, a.dt, a.substeps, a.normalise != 0);
+    if (TRAJ && writer) store_state(VecViewW{Xb + (long long)(k + 1) * a.X_sk, 0, a.X_sc}, 0, s);
+  }
+  if (!writer) return;
+  if (a.xf.base) store_state(a.xf, b, s);
+  if (COST) {
+    const float ex = s.p[0] - a.cc.goal0, ey = s.p[1] - a.cc.goal1, ez = s.p[2] - z0;
+    float J = a.cc.w_goal * (ex * ex + ey * ey);
+    J = fmaf(a.cc.w_du, sum_du, J);
+    J = fmaf(a.cc.w_height, ez * ez, J);
+    J = fmaf(-a.cc.w_speed_over_H, sum_v2, J);
+    J = fmaf(a.cc.vel_param * a.cc.w_vx, s.v[0], J);
+    J = fmaf(a.cc.w_vyz, s.v[1] * s.v[1] + s.v[2] * s.v[2], J);
+    a.cost[b] = J;
+  }
+}
+
 // ------------------------------------------------------------------------------------ K2
 struct LinArgs {
   VecView x, u;

@@ -569,8 +569,11 @@ def side_measurements(torch, ac, dev, rank, args):
         xs, us = trim_states(ac, 4096, seed=rank)
         x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
         U = device_control_sequences(torch, 4096, H_ROLL, seed=200 + rank, device=dev)
-        ms = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True), K, 3, flush)
-        out["c2"] = {"workload": "BASELINE config 2: 4096 rollouts x horizon 200 from trim states, 1 GPU",
+        ms_default = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True), K, 3, flush)
+        ms = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True, cooperative=True), K, 3, flush)
+        out["c2"] = {"workload": "BASELINE config 2: 4096 rollouts x horizon 200 from trim states, 1 GPU; latency mode "
+                                 "(AIRC_FLAG_COOPERATIVE: 4 lanes per trajectory); default one-trajectory kernel under ms_default",
+                     "ms_default": ms_default,
                      "value": 4096 * H_ROLL / (ms * 1e-3), "unit": "state-steps/s", "ms_per_launch": ms,
                      "tflops": 4096 * H_ROLL * F_STEP / (ms * 1e-3) / 1e12, "l2": "flushed between launches"}
 

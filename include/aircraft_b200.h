@@ -54,6 +54,11 @@ extern "C" {
 /* flags */
 #define AIRC_FLAG_NORMALISE 1u   /* q <- q/|q| as base.py:443-444 / :473-474 (opts['quaternion']=='integration') */
 #define AIRC_FLAG_SHARED_U  2u   /* rollout: U is one [H][7] sequence shared by all trajectories */
+#define AIRC_FLAG_COOPERATIVE 4u /* rollout, 'nn' model, B <= 64 x SM count: latency mode -- 8, 4 or 2 lanes share one
+                                  * trajectory (the network's hidden units are split among them).  1.1-1.3x shorter
+                                  * launches for small batches; results differ from the default kernel in the last
+                                  * bits (different summation order), so it is opt-in: a sharded batch is bit-identical
+                                  * to the whole one only while both run the same kernel. */
 
 /* Aircraft constants: AircraftConfiguration (utils.py:201-215), SixDOFOpts (base.py:9-14),
  * AircraftOpts (aircraft.py:22-38).  inertia / inertia_inv are about the shifted CoM

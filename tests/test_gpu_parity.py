@@ -218,3 +218,23 @@ def test_diagnostics_side_functions(ac, orc):
     assert one["v_frd_rel"].shape == (3,) and one["coefficients"].shape == (6,)
     assert abs(float(one["qbar"]) - float(d["qbar"][5])) <= 1e-6 * float(d["qbar"][5])
     assert np.allclose(one["moments_frd"], d["moments_frd"][:, 5].cpu().numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_cooperative_small_batch_rollout(ac, orc):
+    """Latency mode (AIRC_FLAG_COOPERATIVE: 8 / 4 / 2 lanes per trajectory): teacher-forced parity with the oracle
+    at every step for each lane count, run-to-run determinism, agreement with the default kernel to rounding."""
+    from aircraft_b200.workloads import make_control_sequences
+    H = 12
+    for B in (3, 2368, 4000, 9000):                 # 8, 8, 4 and 2 lanes per trajectory on a 148-SM part
+        x0 = make_states(B, seed=81)
+        U = make_control_sequences(B, H, seed=81)
+        a = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True, cost=True, cooperative=True)
+        b = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True, cost=True, cooperative=True)
+        assert torch.equal(a.trajectory, b.trajectory) and torch.equal(a.cost, b.cost)
+        X = a.trajectory.cpu().numpy()
+        xs = X[:, :-1].reshape(-1, 13).astype(np.float64)
+        want = orc.state_update(t64(xs), t64(U.reshape(-1, 7)), 0.01, 1, True).numpy()
+        assert col_err(X[:, 1:].reshape(-1, 13), want) < PARITY_TOL
+        d = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True, cost=True)
+        assert col_err(a.trajectory.cpu(), d.trajectory.cpu().numpy(), batch_axes=(0, 1)) < 2e-5
+        assert col_err(a.cost.cpu()[:, None], d.cost.cpu().numpy()[:, None]) < 1e-5
