@@ -606,8 +606,11 @@ def side_measurements(torch, ac, dev, rank, args):
     # config 1: ONE trajectory x 100 steps (the reference's own CPU-runnable case): latency per step
     x1 = torch.tensor(make_states(1, seed=1, level=True), dtype=torch.float32, device=dev)
     U1 = device_control_sequences(torch, 1, 100, seed=11, device=dev).permute(2, 0, 1).contiguous()   # [1,100,7]
-    ms = time_launches(torch, lambda: ac.rollout(x1, U1, DT, return_trajectory=True), max(K, 20), 3, None)
-    out["c1"] = {"workload": "BASELINE config 1: 1 trajectory x 100 steps, full trajectory returned (latency case)",
+    ms1 = time_launches(torch, lambda: ac.rollout(x1, U1, DT, return_trajectory=True), max(K, 20), 3, None)
+    ms = time_launches(torch, lambda: ac.rollout(x1, U1, DT, return_trajectory=True, cooperative=True), max(K, 20), 3, None)
+    out["c1"] = {"workload": "BASELINE config 1: 1 trajectory x 100 steps, full trajectory returned (latency case); latency "
+                             "mode (AIRC_FLAG_COOPERATIVE, 8 lanes), default kernel under ms_default",
+                 "ms_default": ms1,
                  "value": ms * 1e3 / 100, "unit": "us/state-step", "higher_is_better": False, "ms_per_launch": ms}
     if rank == 0:
         try:
