@@ -118,8 +118,6 @@ def load_library(path: os.PathLike | str | None = None) -> C.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    if path is None and os.environ.get("AIRC_LIB"):     # A/B timing of build variants (profiles/)
-        path = os.environ["AIRC_LIB"]
     p = Path(path) if path else LIB_PATH
     if not p.exists():
         raise ImportError(

@@ -10,6 +10,7 @@
 #include "airc_fuse.hpp"
 #include "airc_kernels.cuh"
 #include "airc_kernels2.cuh"
+#include "airc_jac_kernel.cuh"
 #include "airc_hess.cuh"
 #include "airc_peak.cuh"
 #include "airc_sweep.cuh"
@@ -299,15 +300,43 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
     else linearize_jet_kernel<false, 1><<<gridj, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
     return check_launch();
   }
-#ifdef AIRC_LIN_V1   // round-1 kernel: 16 lanes per node, everything recomputed per lane
-  const long long threads = n * 16;
-  linearize_kernel<<<(unsigned)((threads + bs - 1) / bs), bs, 0, (cudaStream_t)stream>>>(h->dc, a);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (substeps == 1) {
+    // K2, structured form (airc_jac.cuh): one launch configuration per (tile size, layout, dt column)
+    const bool soa = layout == AIRC_LAYOUT_SOA, want_dt = Dt != nullptr;
+    auto al16 = [](const void* p) { return p == nullptr || ((uintptr_t)p & 15u) == 0; };
+    const int vec_ok = (al16(A) && al16(Bm) && al16(Dt) && (!soa || (n & 3) == 0)) ? 1 : 0;
+    // tiles of 128 nodes (one block per SM) once every SM has at least two of them; 64-node tiles below that
+#ifdef AIRC_JAC_FORCE_NT            // build-variant A/B only (profiles/build_variants.py); never set in the shipped build
+    const bool big = AIRC_JAC_FORCE_NT == 128;
 #else
+    const bool big = n >= (int64_t)h->sm_count * 256;
+#endif
+#define AIRC_JAC_LAUNCH(NT_, SOA_, DT_)                                                                     \
+    do {                                                                                                    \
+      using T_ = JacTile<NT_, SOA_, DT_>;                                                                   \
+      CUDA_TRY(cudaFuncSetAttribute(linearize_tile_kernel<NT_, SOA_, DT_>,                                 \
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_::SMEM));          \
+      linearize_tile_kernel<NT_, SOA_, DT_><<<(unsigned)((n + NT_ - 1) / NT_), T_::TPB, T_::SMEM, st>>>(h->dc, a, vec_ok); \
+    } while (0)
+#define AIRC_JAC_PICK(NT_)                                                                                  \
+    do {                                                                                                    \
+      if (soa && want_dt) AIRC_JAC_LAUNCH(NT_, true, true);                                                 \
+      else if (soa) AIRC_JAC_LAUNCH(NT_, true, false);                                                      \
+      else if (want_dt) AIRC_JAC_LAUNCH(NT_, false, true);                                                  \
+      else AIRC_JAC_LAUNCH(NT_, false, false);                                                              \
+    } while (0)
+    if (big) AIRC_JAC_PICK(128);
+    else AIRC_JAC_PICK(64);
+#undef AIRC_JAC_PICK
+#undef AIRC_JAC_LAUNCH
+    return check_launch();
+  }
+  // substeps > 1: the cooperative kernel (8 lanes per node, tangents pushed through f; airc_coop.cuh)
   const long long threads = n * 8;
   const unsigned grid = (unsigned)((threads + bs - 1) / bs);
-  if (layout == AIRC_LAYOUT_SOA) linearize_coop_kernel<8, true><<<grid, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
-  else linearize_coop_kernel<8, false><<<grid, bs, 0, (cudaStream_t)stream>>>(h->dc, a);
-#endif
+  if (layout == AIRC_LAYOUT_SOA) linearize_coop_kernel<8, true><<<grid, bs, 0, st>>>(h->dc, a);
+  else linearize_coop_kernel<8, false><<<grid, bs, 0, st>>>(h->dc, a);
   return check_launch();
 }
 
@@ -320,9 +349,6 @@ int airc_linearize(const AircHandle* h, const float* x, const float* u, float dt
 int airc_linearize_dt(const AircHandle* h, const float* x, const float* u, float dt,
                       const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
                       float* x_next, float* A, float* Bm, float* dPhi_ddt, void* stream) {
-#ifdef AIRC_LIN_V1
-  if (dPhi_ddt) return fail(AIRC_EINVAL, "airc_linearize_dt: not available in the AIRC_LIN_V1 build%s", "");
-#endif
   return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, x_next, A, Bm, dPhi_ddt, stream);
 }
 
@@ -330,9 +356,6 @@ int airc_defects(const AircHandle* h, const float* x, const float* u, const floa
                  const float* dt_per_node, int64_t n, int substeps, uint32_t flags, int layout,
                  float* defect, float* A, float* Bm, float* dPhi_ddt, void* stream) {
   if (!x_target || !defect) return fail(AIRC_EINVAL, "airc_defects: bad argument%s", "");
-#ifdef AIRC_LIN_V1
-  return fail(AIRC_EINVAL, "airc_defects: not available in the AIRC_LIN_V1 build%s", "");
-#endif
   return linearize_impl(h, x, u, dt, dt_per_node, n, substeps, flags, layout, nullptr, A, Bm, dPhi_ddt, stream,
                         x_target, defect);
 }

@@ -4,8 +4,8 @@
 //   K0' state_update_kernel       Phi(x,u,dt) at n nodes                  (base.py:450-480)
 //   K1  rollout_kernel            B trajectories x H steps, state in registers for the whole
 //                                 horizon, optional trajectory write-out and fused cost (K3)
-//   K2  linearize_kernel          (x+, dPhi/dx, dPhi/du) at n nodes, forward mode,
-//                                 one tangent column per lane (16 lanes per node)
+//   K2  linearize_coop_kernel     (x+, dPhi/dx, dPhi/du) at n nodes, forward mode, 8 lanes per node -- serves
+//                                 substeps > 1; the one-substep case runs the tile kernel of airc_jac_kernel.cuh
 //   K3' argmin_kernel             (min, argmin) over costs, warp shuffles + 64-bit atomicMin
 //
 // All global accesses go through explicit element strides so that the same kernels serve the
@@ -333,79 +333,6 @@ struct LinArgs {
   int substeps;
   int normalise;
 };
-
-// 16 lanes per node.  Lanes 0..9 carry the tangent columns of the state components the
-// dynamics depend on (v, q, omega = state indices 3..12), lanes 10..13 the four live control
-// columns (aileron, elevator, rudder, flaps = control indices 0,1,2,6).  f does not read p and
-// thrust is inert (aircraft.py:320), so dPhi/dp = [I;0] and dPhi/du[:,3:6] = 0 exactly: lanes
-// 14 and 15 write those constant columns.  Each lane pushes its column through the four RK4
-// stages (and all substeps) next to the primal, so nothing is exchanged between lanes.
-__global__ void __launch_bounds__(128)
-linearize_kernel(const __grid_constant__ DevConst P, const LinArgs a) {
-  const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long long node = gt >> 4;
-  const int lane = (int)(gt & 15);
-  if (node >= a.n) return;
-  State s;
-  load_state(a.x, node, s);
-  const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
-  const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
-
-  Tangent T;
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    T.p[i] = 0.0f;
-    T.v[i] = (lane == i) ? 1.0f : 0.0f;
-    T.w[i] = (lane == 7 + i) ? 1.0f : 0.0f;
-  }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) T.q[i] = (lane == 3 + i) ? 1.0f : 0.0f;
-  T.dc.da = (lane == 10) ? 1.0f : 0.0f;
-  T.dc.de = (lane == 11) ? 1.0f : 0.0f;
-  T.dc.dr = (lane == 12) ? 1.0f : 0.0f;
-  T.dc.df = (lane == 13) ? 1.0f : 0.0f;
-
-  state_update<1>(P, s, c, dt, a.substeps, a.normalise != 0, &T);
-
-  if (lane == 0 && a.xn.base) store_state(a.xn, node, s);
-
-  float col[13];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) { col[i] = T.p[i]; col[3 + i] = T.v[i]; col[10 + i] = T.w[i]; }
-#pragma unroll
-  for (int i = 0; i < 4; ++i) col[6 + i] = T.q[i];
-
-  if (lane < 10) {
-    if (a.A) {
-      float* o = a.A + node * a.A_sn + (long long)(3 + lane) * a.A_se;
-#pragma unroll
-      for (int r = 0; r < 13; ++r) o[(long long)(r * 13) * a.A_se] = col[r];
-    }
-  } else if (lane < 14) {
-    if (a.Bm) {
-      const int cu = (lane == 13) ? 6 : lane - 10;
-      float* o = a.Bm + node * a.B_sn + (long long)cu * a.B_se;
-#pragma unroll
-      for (int r = 0; r < 13; ++r) o[(long long)(r * 7) * a.B_se] = col[r];
-    }
-  } else if (lane == 14) {
-    if (a.A) {
-      float* o = a.A + node * a.A_sn;
-#pragma unroll
-      for (int r = 0; r < 13; ++r)
-#pragma unroll
-        for (int cc = 0; cc < 3; ++cc) o[(long long)(r * 13 + cc) * a.A_se] = (r == cc) ? 1.0f : 0.0f;
-    }
-  } else {
-    if (a.Bm) {
-      float* o = a.Bm + node * a.B_sn;
-#pragma unroll
-      for (int r = 0; r < 13; ++r)
-#pragma unroll
-        for (int cc = 3; cc < 6; ++cc) o[(long long)(r * 7 + cc) * a.B_se] = 0.0f;
-    }
-  }
-}
 
 // ------------------------------------------------------------------------------------ K2 (cooperative)
 // L = 8 lanes per node, 4 nodes per warp.  Column slots 2*lane, 2*lane+1 (one packed tangent):

@@ -91,27 +91,24 @@ AIRC_D F2 f2_unpack(unsigned long long v) {
 
 AIRC_HD F2 fma2(const F2& a, const F2& b, const F2& c) {
 #if defined(__CUDA_ARCH__)
-  unsigned long long d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)), "l"(f2_pack(c)));
-  return f2_unpack(d);
+  const float2 d = __ffma2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi), make_float2(c.lo, c.hi));
+  return F2{d.x, d.y};
 #else
   return F2{fmaf(a.lo, b.lo, c.lo), fmaf(a.hi, b.hi, c.hi)};
 #endif
 }
 AIRC_HD F2 add2(const F2& a, const F2& b) {
 #if defined(__CUDA_ARCH__)
-  unsigned long long d;
-  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
-  return f2_unpack(d);
+  const float2 d = __fadd2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi));
+  return F2{d.x, d.y};
 #else
   return F2{a.lo + b.lo, a.hi + b.hi};
 #endif
 }
 AIRC_HD F2 mul2(const F2& a, const F2& b) {
 #if defined(__CUDA_ARCH__)
-  unsigned long long d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
-  return f2_unpack(d);
+  const float2 d = __fmul2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi));
+  return F2{d.x, d.y};
 #else
   return F2{a.lo * b.lo, a.hi * b.hi};
 #endif

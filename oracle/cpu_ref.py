@@ -174,6 +174,19 @@ class HostEmul:
                                        substeps, 1 if normalise else 0, xn, A, Bm)
         return xn, A, Bm
 
+    def linearize_tile(self, x, u, dt, normalise=False, want_dt=False):
+        """The tile kernel's arithmetic (airc_jac.cuh: parked f_x / f_u blocks + tangent recursion), one substep."""
+        x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)
+        n = x.shape[0]
+        xn = np.empty((n, 13), np.float32)
+        A, Bm = np.zeros((n, 13, 13), np.float32), np.zeros((n, 13, 7), np.float32)
+        Dt = np.zeros((n, 13), np.float32) if want_dt else None
+        self.lib.emul_linearize_tile.argtypes = [_PP, _NP, _f32, _f32, C.c_float, C.c_int64, C.c_uint32, _f32, _f32,
+                                                 _f32, C.c_void_p]
+        self.lib.emul_linearize_tile(C.byref(self.params), C.byref(self.blob), x, u, float(dt), n,
+                                     1 if normalise else 0, xn, A, Bm, None if Dt is None else Dt.ctypes.data)
+        return (xn, A, Bm, Dt) if want_dt else (xn, A, Bm)
+
     def model_state_update(self, model, table, x, u, dt, substeps=1, normalise=False):
         """airc_alt.cuh (poly / linear / default coefficient models) through the product's RK4."""
         x, u = np.ascontiguousarray(x, np.float32), np.ascontiguousarray(u, np.float32)

@@ -12,6 +12,7 @@
 #include "../aircraft_b200/csrc/airc_coop.cuh"
 #include "../aircraft_b200/csrc/airc_sampler.cuh"
 #include "../aircraft_b200/csrc/airc_hess.cuh"
+#include "../aircraft_b200/csrc/airc_jac.cuh"
 
 using namespace airc;
 
@@ -151,6 +152,44 @@ void emul_linearize_packed_dt(const AircParams* p, const AircNNBlob* nn, const f
                               float dt, int64_t n, int substeps, uint32_t flags, float* xn, float* A,
                               float* Bm, float* Dt) {
   linearize_packed_impl(p, nn, x, u, dt, n, substeps, flags, xn, A, Bm, Dt);
+}
+
+// The tile kernel's arithmetic (airc_jac.cuh): phase 1 parks the f_x / f_u blocks of the four stage points in a
+// node record, phase 2 runs the tangent recursion per column pair.  One substep.  A[n][13][13], B[n][13][7],
+// Dt[n][13] (may be NULL).
+void emul_linearize_tile(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, float dt,
+                         int64_t n, uint32_t flags, float* xn, float* A, float* Bm, float* Dt) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  const bool norm = flags & AIRC_FLAG_NORMALISE;
+  for (int64_t i = 0; i < n; ++i) {
+    alignas(16) float rec[JRec<true>::NODE];
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    if (Dt) jac_phase1<true>(P, s, c, dt, rec);
+    else jac_phase1<false>(P, s, c, dt, rec);
+    if (norm) normalise_q<0>(s, nullptr);
+    store(s, xn + 13 * i);
+    static const int bcol[4] = {0, 1, 2, 6};
+    for (int pair = 0; pair < (Dt ? 8 : 7); ++pair) {
+      F2 col[13];
+      if (Dt) jac_phase2<true>(rec, pair, norm, col);
+      else jac_phase2<false>(rec, pair, norm, col);
+      for (int r = 0; r < 13; ++r) {
+        const float vals[2] = {col[r].lo, col[r].hi};
+        for (int hlf = 0; hlf < 2; ++hlf) {
+          const int slot = 2 * pair + hlf;
+          if (slot < 10) A[(i * 13 + r) * 13 + 3 + slot] = vals[hlf];
+          else if (slot < 14) Bm[(i * 13 + r) * 7 + bcol[slot - 10]] = vals[hlf];
+          else if (slot == 14) Dt[i * 13 + r] = vals[hlf];
+        }
+      }
+    }
+    for (int r = 0; r < 13; ++r) {
+      for (int cc = 0; cc < 3; ++cc) A[(i * 13 + r) * 13 + cc] = (r == cc) ? 1.0f : 0.0f;
+      for (int cc = 3; cc < 6; ++cc) Bm[(i * 13 + r) * 7 + cc] = 0.0f;
+    }
+  }
 }
 
 // the registry's other coefficient models (airc_alt.cuh) through the product's f / RK4

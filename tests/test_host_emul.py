@@ -124,3 +124,33 @@ def test_lagrangian_hessian_jets_stall_scaling(built):
     H, g, v = emu.hessian(x, u, lam, 0.01)
     Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.01))
     assert col_err(H, Ho, atol=1e-3) < PARITY_TOL and col_err(g, go) < PARITY_TOL
+
+
+@pytest.mark.parametrize("normalise", [False, True])
+def test_linearize_tile_structured_jacobian(pair, normalise):
+    """The tile kernel's arithmetic (airc_jac.cuh): f_x / f_u blocks assembled once per stage point from the
+    chain (v,q) -> v_b -> (qbar, alpha, beta) -> C -> (F, M), parked, then the RK4 tangent recursion as small
+    matrix products -- against jacfwd of the float64 oracle, incl. the d/d(dt) column."""
+    emu, orc = pair
+    x, u = make_states(512, seed=29, perturb_norm=1e-3), make_controls(512, seed=29)
+    xn, A, B, Dt = emu.linearize_tile(x, u, 0.02, normalise, want_dt=True)
+    xo, Ao, Bo, Do = orc.linearize(t64(x), t64(u), 0.02, 1, normalise, want_dt=True)
+    assert col_err(xn, xo.numpy()) < PARITY_TOL
+    assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(Dt, Do.numpy(), atol=1e-3) < PARITY_TOL
+    x2, A2, B2 = emu.linearize_tile(x, u, 0.02, normalise)
+    assert np.array_equal(A, A2) and np.array_equal(B, B2) and np.array_equal(xn, x2)
+    eye = np.eye(13, dtype=np.float32)[:, :3]
+    assert np.array_equal(A[:, :, :3], np.broadcast_to(eye, (512, 13, 3))) and not B[:, :, 3:6].any()
+
+
+def test_linearize_tile_with_stall_scaling(built):
+    p, blob = params_for(stall_scaling=True)
+    emu, orc = HostEmul(p, blob), oracle_for(stall_scaling=True)
+    x, u = make_states(256, seed=30), make_controls(256, seed=30)
+    x[:128, 3:6] *= np.array([0.6, 1.0, 2.0])
+    xn, A, B = emu.linearize_tile(x, u, 0.01)
+    xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01)
+    assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
+    assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
