@@ -9,7 +9,7 @@ from pathlib import Path
 
 NX, NU = 13, 7
 LAYOUT_SOA, LAYOUT_AOS = 0, 1
-FLAG_NORMALISE, FLAG_SHARED_U, FLAG_COOPERATIVE = 1, 2, 4
+FLAG_NORMALISE, FLAG_SHARED_U, FLAG_COOPERATIVE, FLAG_PACKED = 1, 2, 4, 8
 OK, EINVAL, ECUDA, ENODEV, ENOMEM, EUNSUPPORTED = 0, -1, -2, -3, -4, -5
 MODEL_POLY, MODEL_LINEAR, MODEL_DEFAULT = 1, 2, 3
 

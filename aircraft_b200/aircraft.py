@@ -26,7 +26,7 @@ from typing import Any, Callable, Dict, Optional, Sequence
 import numpy as np
 
 from . import _cabi
-from ._cabi import (FLAG_COOPERATIVE, FLAG_NORMALISE, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX, NZ)
+from ._cabi import (FLAG_COOPERATIVE, FLAG_NORMALISE, FLAG_PACKED, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX, NZ)
 from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH)
 from .params import (load_linear_model, load_nn_blob, load_poly_model, make_cost_params, make_params,
@@ -441,7 +441,7 @@ class Aircraft:
     def rollout(self, x0, U, dt: float, *, substeps: Optional[int] = None,
                 normalise: Optional[bool] = None, layout: str = "aos",
                 return_trajectory: bool = False, return_final: bool = True,
-                cost=None, cooperative: bool = False) -> RolloutResult:
+                cost=None, cooperative: bool = False, packed: bool = False) -> RolloutResult:
         """x[k+1] = Phi(x[k], u[k], dt) for k < H over B independent trajectories in ONE kernel:
         the reference's Python loops (main/control/control.py:84-90,
         control/moving_horizon.py:208-213, main/dynamics/dynamics.py:105-121).
@@ -454,6 +454,8 @@ class Aircraft:
               AircCostParams -> per-trajectory primary MPC loss (main/control/control.py:35-70).
         cooperative: latency mode for small batches (B <= 64 x SM count, 'nn' model): several lanes share one
               trajectory (AIRC_FLAG_COOPERATIVE); last-bit differences from the default kernel.
+        packed: run the two-trajectories-per-thread kernel (the sweep's arithmetic, AIRC_FLAG_PACKED) whatever the
+              batch size; by default it serves batches of two waves and more.
         """
         if layout not in ("aos", "soa"):
             raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
@@ -467,7 +469,7 @@ class Aircraft:
         if x0d.ndim != 2 or x0d.shape[0 if soa else 1] != NX:
             raise RuntimeError(f"x0 must be {'[13,B]' if soa else '[B,13]'}, got {tuple(x0d.shape)}")
         B = x0d.shape[1 if soa else 0]
-        flags = self._flags(normalise) | (FLAG_COOPERATIVE if cooperative else 0)
+        flags = self._flags(normalise) | (FLAG_COOPERATIVE if cooperative else 0) | (FLAG_PACKED if packed else 0)
         if Ud.ndim == 2:
             if Ud.shape[1] != NU:
                 raise RuntimeError(f"shared control sequence must be [H,7], got {tuple(Ud.shape)}")

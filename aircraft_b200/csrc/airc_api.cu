@@ -21,8 +21,8 @@ using namespace airc;
 struct AircHandle {
   DevConst dc;
   UnitNet un;          // the surrogate in unit-major order for the packed (two-trajectory) kernels
-  int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0 / 2: force scalar / packed
-  int coop = 0;        // AIRC_ROLLOUT_COOP=1|2|4|8: small-batch rollouts on the lanes-per-trajectory kernel without the flag
+  int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0: table models (scalar kernels only)
+  int coop = 0;        // non-zero only in A/B build variants (small-batch rollouts on the lanes-per-trajectory kernel)
   int device;
   int sm_count;
   // used only by the *_host entry points (those are not re-entrant per handle)
@@ -101,11 +101,12 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   if (!h) return fail(AIRC_ENOMEM, "airc_create: out of host memory%s", "");
   build_devconst(*params, *nn, h->dc);
   make_unit_net(h->dc.net, h->un);
-  if (const char* e = getenv("AIRC_ROLLOUT_IMPL")) h->packed = atoi(e) == 1 ? 0 : 2;   // 0 scalar only, 1 auto, 2 packed always
-  if (const char* e = getenv("AIRC_ROLLOUT_COOP")) {   // 0 off, 1 auto, 2/4/8 force that many lanes (A/B timing)
-    const int v = atoi(e);
-    h->coop = (v == 0 || v == 1 || v == 2 || v == 4 || v == 8) ? v : 1;
-  }
+#ifdef AIRC_AB_ROLLOUT_IMPL        // build-variant A/B only (profiles/build_variants.py): 0 scalar only, 2 packed always
+  h->packed = AIRC_AB_ROLLOUT_IMPL;
+#endif
+#ifdef AIRC_AB_ROLLOUT_COOP        // build-variant A/B only: 1 auto, 2/4/8 force that many lanes per trajectory
+  h->coop = AIRC_AB_ROLLOUT_COOP;
+#endif
   h->device = device;
   h->sm_count = prop.multiProcessorCount;
   *out = h;
@@ -197,7 +198,7 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
                  int H, int substeps, uint32_t flags, int layout, float* X, float* x_final,
                  float* cost, const AircCostParams* cp, void* stream) {
   if (!h || B < 0 || H < 0 || substeps < 1 || (layout != 0 && layout != 1) ||
-      (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U | AIRC_FLAG_COOPERATIVE)) || (cost && !cp))
+      (flags & ~(uint32_t)(AIRC_FLAG_NORMALISE | AIRC_FLAG_SHARED_U | AIRC_FLAG_COOPERATIVE | AIRC_FLAG_PACKED)) || (cost && !cp))
     return fail(AIRC_EINVAL, "airc_rollout: bad argument%s", "");
   if (B == 0) return AIRC_OK;   // empty batch: nothing to read, so NULL data pointers are fine
   if (!x0 || (!U && H > 0)) return fail(AIRC_EINVAL, "airc_rollout: NULL x0 or U%s", "");
@@ -257,7 +258,7 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
 #undef AIRC_COOP_LAUNCH
     return check_launch();
   }
-  if (h->packed == 2 || (h->packed == 1 && B >= 2 * wave2)) {
+  if (h->packed == 2 || (h->packed == 1 && ((flags & AIRC_FLAG_PACKED) || B >= 2 * wave2))) {
     const unsigned grid2 = (unsigned)((B + 2 * AIRC_R2_BS - 1) / (2 * AIRC_R2_BS));
     if (cost && X) rollout2_kernel<true, true><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
     else if (cost) rollout2_kernel<true, false><<<grid2, AIRC_R2_BS, 0, st>>>(h->dc, h->un, a);
@@ -521,7 +522,9 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
     const int bs = (a.G <= slots) ? 32 : AIRC_S2_BS;
     a.GB = (a.G + bs / 32 - 1) / (bs / 32);
     a.S = full ? choose_segments(a.GB, bs == 32 ? slots * (AIRC_S2_BS / 32) : slots, H) : 1;
-    if (const char* e = getenv("AIRC_SWEEP_SEGMENTS")) { if (full && atoi(e) > 0) a.S = atoi(e); }   // timing experiments
+#ifdef AIRC_AB_SWEEP_SEGMENTS      // build-variant A/B only
+    if (full) a.S = AIRC_AB_SWEEP_SEGMENTS;
+#endif
     a.L = a.S > 1 ? (H + a.S - 1) / a.S : (H > 0 ? H : 1);
     a.S = H > 0 ? (H + a.L - 1) / a.L : 1;
     a.x0 = x0; a.Unom = U_nom; a.cost = cost; a.key = key; a.thrust_du = thrust_du;

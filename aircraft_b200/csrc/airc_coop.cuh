@@ -29,7 +29,7 @@ AIRC_HD F2 group_sum2(F2 v) {
 #if defined(__CUDA_ARCH__)
 #pragma unroll
   for (int off = L / 2; off > 0; off >>= 1)
-    v = add2(v, F2{__shfl_xor_sync(0xFFFFFFFFu, v.lo, off), __shfl_xor_sync(0xFFFFFFFFu, v.hi, off)});
+    v = add2b(v, F2{__shfl_xor_sync(0xFFFFFFFFu, v.lo, off), __shfl_xor_sync(0xFFFFFFFFu, v.hi, off)});
 #endif
   return v;
 }
@@ -58,14 +58,14 @@ struct NetCoop {
         const int p = vl + m * V;
         const HidPair& w = net->hid[p];
         F2 h = F2{w.a0[0], w.a0[1]};
-        h = fma2(F2{w.Au[0][0], w.Au[0][1]}, da, h);
-        h = fma2(F2{w.Au[1][0], w.Au[1][1]}, de, h);
-        h = fma2(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
-        h = fma2(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
-        h = fma2(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+        h = fma2b(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+        h = fma2b(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+        h = fma2b(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+        h = fma2b(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+        h = fma2b(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
         const F2 r = sigm2_x2(h);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) acc[k] = fma2(F2{net->Wo[k][2 * p], net->Wo[k][2 * p + 1]}, r, acc[k]);
+        for (int k = 0; k < 6; ++k) acc[k] = fma2b(F2{net->Wo[k][2 * p], net->Wo[k][2 * p + 1]}, r, acc[k]);
       }
 #pragma unroll
       for (int kk = 0; kk < 3; ++kk)
@@ -77,7 +77,7 @@ struct NetCoop {
 #pragma unroll
       for (int j = 0; j < st; ++j)
 #pragma unroll
-        for (int kk = 0; kk < 3; ++kk) part[j][kk] = add2(part[j][kk], part[j + st][kk]);
+        for (int kk = 0; kk < 3; ++kk) part[j][kk] = add2b(part[j][kk], part[j + st][kk]);
     }
 #pragma unroll
     for (int kk = 0; kk < 3; ++kk) {
@@ -106,25 +106,25 @@ struct NetCoop {
       const int p = lane + m * L;
       const HidPair& w = net->hid[p];
       F2 h = F2{w.a0[0], w.a0[1]};
-      h = fma2(F2{w.Au[0][0], w.Au[0][1]}, da, h);
-      h = fma2(F2{w.Au[1][0], w.Au[1][1]}, de, h);
-      h = fma2(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
-      h = fma2(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
-      h = fma2(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+      h = fma2b(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+      h = fma2b(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+      h = fma2b(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+      h = fma2b(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+      h = fma2b(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
       const F2 r = sigm2_x2(h);
-      const F2 g = mul2(mul2(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
+      const F2 g = mul2b(mul2b(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
       F2 wo[6];
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
         wo[k] = F2{net->Wo[k][2 * p], net->Wo[k][2 * p + 1]};
-        acc[k] = fma2(wo[k], r, acc[k]);
+        acc[k] = fma2b(wo[k], r, acc[k]);
       }
 #pragma unroll
       for (int i = 0; i < 5; ++i) {
         const F2 wi = (i < 3) ? F2{w.Ax[i][0], w.Ax[i][1]} : F2{w.Au[i - 3][0], w.Au[i - 3][1]};
-        const F2 gw = mul2(g, wi);
+        const F2 gw = mul2b(g, wi);
 #pragma unroll
-        for (int k = 0; k < 6; ++k) Jacc[k][i] = fma2(wo[k], gw, Jacc[k][i]);
+        for (int k = 0; k < 6; ++k) Jacc[k][i] = fma2b(wo[k], gw, Jacc[k][i]);
       }
     }
     // 36 sums = 18 packed pairs: (C[k], J[k][0]) and (J[k][1], J[k][2]), (J[k][3], J[k][4])

@@ -139,24 +139,24 @@ AIRC_HD void surrogate(const FusedNet& net, float qbar, float alpha, float beta,
   for (int p = 0; p < NH / 2; ++p) {
     const HidPair& w = net.hid[p];
     F2 h = F2{w.a0[0], w.a0[1]};
-    h = fma2(F2{w.Au[0][0], w.Au[0][1]}, da, h);
-    h = fma2(F2{w.Au[1][0], w.Au[1][1]}, de, h);
-    h = fma2(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
-    h = fma2(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
-    h = fma2(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+    h = fma2b(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+    h = fma2b(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+    h = fma2b(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+    h = fma2b(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+    h = fma2b(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
     const F2 r = sigm2_x2(h);   // AIRC_SIGM_MODE selects the variant (airc_math.cuh)
 #pragma unroll
-    for (int k = 0; k < 6; ++k) acc[k] = fma2(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, r, acc[k]);
+    for (int k = 0; k < 6; ++k) acc[k] = fma2b(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, r, acc[k]);
     if (WITH_JAC) {
       // g_j = d r_j / d h_j = -ln2 r (1 - r)
-      const F2 g = mul2(mul2(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
+      const F2 g = mul2b(mul2b(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
 #pragma unroll
       for (int i = 0; i < 5; ++i) {
         const F2 wi = (i < 3) ? F2{w.Ax[i][0], w.Ax[i][1]} : F2{w.Au[i - 3][0], w.Au[i - 3][1]};
-        const F2 gw = mul2(g, wi);
+        const F2 gw = mul2b(g, wi);
 #pragma unroll
         for (int k = 0; k < 6; ++k)
-          Jacc[k][i] = fma2(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, gw, Jacc[k][i]);
+          Jacc[k][i] = fma2b(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, gw, Jacc[k][i]);
       }
     }
   }

@@ -48,6 +48,27 @@ AIRC_HD float fast_rsqrt(float x) {
 #endif
 }
 
+// min / max that PROPAGATE NaN (fminf / fmaxf return the other operand): a NaN command or state must reach the
+// results, as it does through CasADi's tanh / fmin in the reference (main/dynamics/dynamics.py:108 checks for it).
+AIRC_HD float min_nan(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+#else
+  return (a != a) ? a : ((b != b) ? b : (a < b ? a : b));
+#endif
+}
+AIRC_HD float max_nan(float a, float b) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+  return r;
+#else
+  return (a != a) ? a : ((b != b) ? b : (a > b ? a : b));
+#endif
+}
+
 // 1/x to <= 1 ulp: MUFU.RCP seed + one Newton step on the FMA pipe.
 AIRC_HD float rcp_nr(float x) {
   float r = fast_rcp(x);
@@ -89,7 +110,39 @@ AIRC_D F2 f2_unpack(unsigned long long v) {
 }
 #endif
 
+// Two spellings of the same three instructions.  fma2 / add2 / mul2 are inline PTX: the form the packed rollout
+// kernels (airc_packed.cuh) were tuned with -- ptxas then keeps the weights in uniform registers with the fewest
+// moves.  fma2b / add2b / mul2b are the CUDA 12.8+ builtins: identical arithmetic, but the front end handles
+// thousands of them per function in seconds where the same number of asm statements takes minutes, so the
+// surrogate-with-Jacobian and the tangent code (airc_dynamics.cuh, airc_jac.cuh, tfma vocabulary) use these.
 AIRC_HD F2 fma2(const F2& a, const F2& b, const F2& c) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)), "l"(f2_pack(c)));
+  return f2_unpack(d);
+#else
+  return F2{fmaf(a.lo, b.lo, c.lo), fmaf(a.hi, b.hi, c.hi)};
+#endif
+}
+AIRC_HD F2 add2(const F2& a, const F2& b) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+  return f2_unpack(d);
+#else
+  return F2{a.lo + b.lo, a.hi + b.hi};
+#endif
+}
+AIRC_HD F2 mul2(const F2& a, const F2& b) {
+#if defined(__CUDA_ARCH__)
+  unsigned long long d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+  return f2_unpack(d);
+#else
+  return F2{a.lo * b.lo, a.hi * b.hi};
+#endif
+}
+AIRC_HD F2 fma2b(const F2& a, const F2& b, const F2& c) {
 #if defined(__CUDA_ARCH__)
   const float2 d = __ffma2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi), make_float2(c.lo, c.hi));
   return F2{d.x, d.y};
@@ -97,7 +150,7 @@ AIRC_HD F2 fma2(const F2& a, const F2& b, const F2& c) {
   return F2{fmaf(a.lo, b.lo, c.lo), fmaf(a.hi, b.hi, c.hi)};
 #endif
 }
-AIRC_HD F2 add2(const F2& a, const F2& b) {
+AIRC_HD F2 add2b(const F2& a, const F2& b) {
 #if defined(__CUDA_ARCH__)
   const float2 d = __fadd2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi));
   return F2{d.x, d.y};
@@ -105,7 +158,7 @@ AIRC_HD F2 add2(const F2& a, const F2& b) {
   return F2{a.lo + b.lo, a.hi + b.hi};
 #endif
 }
-AIRC_HD F2 mul2(const F2& a, const F2& b) {
+AIRC_HD F2 mul2b(const F2& a, const F2& b) {
 #if defined(__CUDA_ARCH__)
   const float2 d = __fmul2_rn(make_float2(a.lo, a.hi), make_float2(b.lo, b.hi));
   return F2{d.x, d.y};
@@ -119,17 +172,17 @@ AIRC_HD F2 bc2(float a) { return F2{a, a}; }
 // forward-mode tangent code is written once.  Primal quantities stay scalar and enter packed
 // instructions as broadcast operands (free in SASS: "R.F32" operand form of FFMA2).
 AIRC_HD float tfma(float a, float b, float c) { return fmaf(a, b, c); }
-AIRC_HD F2 tfma(float a, const F2& b, const F2& c) { return fma2(bc2(a), b, c); }
-AIRC_HD F2 tfma(const F2& a, float b, const F2& c) { return fma2(a, bc2(b), c); }
-AIRC_HD F2 tfma(const F2& a, const F2& b, const F2& c) { return fma2(a, b, c); }
+AIRC_HD F2 tfma(float a, const F2& b, const F2& c) { return fma2b(bc2(a), b, c); }
+AIRC_HD F2 tfma(const F2& a, float b, const F2& c) { return fma2b(a, bc2(b), c); }
+AIRC_HD F2 tfma(const F2& a, const F2& b, const F2& c) { return fma2b(a, b, c); }
 AIRC_HD float tmul(float a, float b) { return a * b; }
-AIRC_HD F2 tmul(float a, const F2& b) { return mul2(bc2(a), b); }
-AIRC_HD F2 tmul(const F2& a, float b) { return mul2(a, bc2(b)); }
-AIRC_HD F2 tmul(const F2& a, const F2& b) { return mul2(a, b); }
+AIRC_HD F2 tmul(float a, const F2& b) { return mul2b(bc2(a), b); }
+AIRC_HD F2 tmul(const F2& a, float b) { return mul2b(a, bc2(b)); }
+AIRC_HD F2 tmul(const F2& a, const F2& b) { return mul2b(a, b); }
 AIRC_HD float tadd(float a, float b) { return a + b; }
-AIRC_HD F2 tadd(const F2& a, const F2& b) { return add2(a, b); }
+AIRC_HD F2 tadd(const F2& a, const F2& b) { return add2b(a, b); }
 AIRC_HD float tsub(float a, float b) { return a - b; }
-AIRC_HD F2 tsub(const F2& a, const F2& b) { return fma2(bc2(-1.0f), b, a); }
+AIRC_HD F2 tsub(const F2& a, const F2& b) { return fma2b(bc2(-1.0f), b, a); }
 template <class T> AIRC_HD T tzero();
 template <> AIRC_HD float tzero<float>() { return 0.0f; }
 template <> AIRC_HD F2 tzero<F2>() { return F2{0.0f, 0.0f}; }
@@ -142,11 +195,12 @@ template <class T> AIRC_HD T tsum(float a, const T& b, float c, const T& d) { re
 // The factor 2*log2(e) is folded into the first-layer weights and the affine map t -> r into
 // the output layer (see fuse_network in airc_api.cu), so the kernels only ever need r.
 // h is clamped at +40 (tanh saturated to < 1 ulp beyond |a| > 9.1; clamp at a = 13.9) so that
-// the product of two denominators cannot overflow in the shared-reciprocal form below.
+// the product of two denominators cannot overflow in the shared-reciprocal form below.  The clamp
+// is NaN-preserving (min_nan): a NaN input makes every pre-activation NaN and must come out as NaN.
 #define AIRC_H_CLAMP 40.0f
 
 AIRC_HD float sigm2(float h) {
-  float e = fast_ex2(fminf(h, AIRC_H_CLAMP));
+  float e = fast_ex2(min_nan(h, AIRC_H_CLAMP));
   return fast_rcp(1.0f + e);
 }
 
@@ -163,10 +217,10 @@ AIRC_HD float sigm2(float h) {
 #endif
 AIRC_HD F2 sigm2_x2(const F2& h) {
 #if AIRC_SIGM_MODE == 0
-  const F2 d = add2(F2{fast_ex2(h.lo), fast_ex2(h.hi)}, F2{1.0f, 1.0f});
+  const F2 d = add2b(F2{fast_ex2(h.lo), fast_ex2(h.hi)}, F2{1.0f, 1.0f});
   return F2{fast_rcp(d.lo), fast_rcp(d.hi)};
 #else  // shared reciprocal (3 MUFU per pair), needs the clamp so that d0*d1 stays finite
-  const F2 d = add2(F2{fast_ex2(fminf(h.lo, 40.0f)), fast_ex2(fminf(h.hi, 40.0f))}, F2{1.0f, 1.0f});
+  const F2 d = add2b(F2{fast_ex2(min_nan(h.lo, 40.0f)), fast_ex2(min_nan(h.hi, 40.0f))}, F2{1.0f, 1.0f});
   const float inv = fast_rcp(d.lo * d.hi);
   return F2{d.hi * inv, d.lo * inv};
 #endif
@@ -174,8 +228,8 @@ AIRC_HD F2 sigm2_x2(const F2& h) {
 
 // two logistic values with ONE reciprocal (Montgomery's trick): 3 MUFU instead of 4.
 AIRC_HD void sigm2_pair(float h0, float h1, float& r0, float& r1) {
-  float d0 = 1.0f + fast_ex2(fminf(h0, AIRC_H_CLAMP));
-  float d1 = 1.0f + fast_ex2(fminf(h1, AIRC_H_CLAMP));
+  float d0 = 1.0f + fast_ex2(min_nan(h0, AIRC_H_CLAMP));
+  float d1 = 1.0f + fast_ex2(min_nan(h1, AIRC_H_CLAMP));
   float inv = fast_rcp(d0 * d1);
   r0 = d1 * inv;
   r1 = d0 * inv;

@@ -52,7 +52,7 @@ AIRC_HD void sample_step(const Sampler& S, unsigned int tkey, int k, const float
     d[c] = (k == 0) ? S.s0[c] * n : fmaf(S.s[c], n, d[c]);
     const float t = unom_k[live_chan(c)] + d[c];
 #endif
-    un[c] = fminf(fmaxf(t, S.lo[c]), S.hi[c]);
+    un[c] = min_nan(max_nan(t, S.lo[c]), S.hi[c]);     // NaN in the nominal sequence stays NaN
   }
 }
 

@@ -4,12 +4,14 @@
 // 64 trajectories; a B200 holds W = 148 x 12 warps = 113 664 trajectories at once.  BASELINE config
 // 4's shard (125 000) is 1.1 "waves": launched plainly, the 11 336 left-over trajectories run
 // almost alone for a whole horizon and cost as much as the full first wave (2.96 ms instead of
-// 2.2 ms x 1.1).  Here the horizon is cut into S segments and the (segment, group) tasks are blocks in
-// segment-major index order, which the hardware hands to warp slots as they free up; a group's state round-trips through
+// 2.2 ms x 1.1).  Here the horizon is cut into S segments and the (segment, group) tasks are taken by the blocks in
+// segment-major order as warp slots free up; a group's state round-trips through
 // a 23-float slice record in HBM between segments (traffic ~1 % of the kernel's time).  All warps
 // stay busy until the very end: makespan ~ ceil(G S / W)/S waves instead of ceil(G / W).
-// A task (s, g) waits on flag[g] >= s; its predecessor (s-1, g) has a lower block index, was dispatched
-// earlier, and is therefore running on a resident warp or done -- no deadlock whatever the residency.
+// A task (s, g) waits on flag[g] >= s; its predecessor (s-1, g) has a lower block index and is normally resident
+// or done.  The wait is BOUNDED: if the hand-over does not arrive, the warp rolls its group forward from x0 itself
+// (and does not publish, so the slice record keeps a single writer chain): termination and results do not depend
+// on the hardware's dispatch order, only the speed does.
 #pragma once
 #include "airc_kernels2.cuh"
 #include "airc_sweep.cuh"
@@ -70,15 +72,25 @@ AIRC_D void stcg2(float* p, long long i0, long long i1, const F2& v, bool live0,
 #ifndef AIRC_S2_MINBLOCKS
 #define AIRC_S2_MINBLOCKS 3
 #endif
+// polls (128 ns sleep each + one L2 round trip) before a task stops waiting for its predecessor: ~50 ms, two
+// orders of magnitude above a segment's duration.  0 in the A/B variant that exercises the fallback on every task.
+#ifndef AIRC_S2_SPIN_LIMIT
+#define AIRC_S2_SPIN_LIMIT 32768u
+#endif
 
 // every WARP is an independent worker (no block-level synchronisation); lanes carry trajectories gs*g + lane (lo) and, when gs = 64, gs*g + 32 + lane (hi)
 template <bool CKPT>
 __global__ void __launch_bounds__(AIRC_S2_BS, AIRC_S2_MINBLOCKS)
 sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNet N, const Sweep2Args a) {
-  // One (segment, 4 groups) task per block, taken from blockIdx: the hardware dispatches blocks in
-  // index order as slots free up, which IS the segment-major dynamic queue.  (A software queue in a
-  // persistent loop makes the step loop's bounds warp-variant for the compiler, which then moves the
-  // network weights from uniform registers (LDCU) to per-thread LDC loads: 30 % slower.)
+  // One (segment, 4 groups) task per block, taken from blockIdx in segment-major order: the hardware dispatches
+  // blocks in index order as slots free up, which IS the dynamic queue, and a task's predecessor (seg-1, same
+  // groups) has a lower index, so normally it is resident or done when the task starts.  CUDA does not
+  // GUARANTEE that order, so nothing here depends on it for correctness or termination: the wait below is
+  // bounded, and a warp whose predecessor has not delivered in time rolls its group forward from x0 itself
+  // (same arithmetic, bit-identical state).
+  // (Measured alternatives, profiles/r2_variants_sweep.txt: tasks handed out by an atomic ticket -- 5 % slower
+  // although the instruction mix is the same; a software queue in a persistent loop -- the step loop's bounds
+  // become warp-variant for the compiler and the weights leave the uniform registers, 30 %.)
   const int lane = threadIdx.x & 31;
   const int seg = (int)(blockIdx.x / (unsigned int)a.GB);
   const int g = (int)(blockIdx.x - (unsigned int)seg * (unsigned int)a.GB) * (int)(blockDim.x >> 5) + (int)(threadIdx.x >> 5);
@@ -87,11 +99,28 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
     const long long r0 = (long long)a.gs * g + lane, r1 = r0 + 32;
     const bool live0 = r0 < a.B, live1 = a.gs == 64 && r1 < a.B;
     const long long b0 = live0 ? r0 : a.B - 1, b1 = live1 ? r1 : a.B - 1;
-    const int k0 = seg * a.L, k1 = min(a.H, k0 + a.L);
+    const int kown = seg * a.L, k1 = min(a.H, kown + a.L);   // this task owns steps [kown, k1)
+    int k0 = kown;
+    bool from_x0 = seg == 0, fell_back = false;
+    if (!from_x0) {
+      // Bounded wait for the predecessor's hand-over.  Every condition is a warp VOTE, i.e. warp-uniform BY
+      // CONSTRUCTION: with a spin loop that only lane 0 runs, ptxas treats everything after it as divergent and
+      // stops using uniform registers for the network weights (LDC + R.F32 broadcasts instead of LDCU + UR.F32:
+      // 30 % slower).
+      unsigned int spins = 0;
+      while (__any_sync(0xFFFFFFFFu, *(volatile int*)(a.flag + g) < seg && spins < AIRC_S2_SPIN_LIMIT)) {
+        __nanosleep(128);
+        ++spins;
+      }
+      if (__any_sync(0xFFFFFFFFu, *(volatile int*)(a.flag + g) < seg)) {
+        from_x0 = fell_back = true;        // not delivered: do the earlier segments ourselves
+        k0 = 0;
+      }
+    }
 
     State2 s;
     F2 d[4], up[4], sum_du, sum_v2;
-    if (seg == 0) {
+    if (from_x0) {
       State s1;
       load_state_uniform(a.x0, s1);
 #pragma unroll
@@ -101,10 +130,6 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
       sum_du = bc2(0.0f);
       sum_v2 = bc2(0.0f);
     } else {
-      // the exit condition is a warp vote, i.e. warp-uniform BY CONSTRUCTION: with a spin loop that
-      // only lane 0 runs, ptxas treats everything after it as divergent and stops using uniform
-      // registers for the network weights (LDC + R.F32 broadcasts instead of LDCU + UR.F32: 30 % slower)
-      while (__any_sync(0xFFFFFFFFu, *(volatile int*)(a.flag + g) < seg)) __nanosleep(128);
       __threadfence();
       const float* sl = a.slice;
 #pragma unroll
@@ -127,6 +152,8 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
 #pragma unroll 1
     for (int k = k0; k < k1; ++k) {
       if (CKPT) {
+        // (a task that fell back rewrites the earlier segments' checkpoints with the same bits: skipping them with
+        //  `k >= kown` costs 4 % of the whole kernel -- the loop counter then leaves the uniform datapath)
         if (k > 0 && (k % a.C) == 0) {
           float* ck = a.ckpt + (long long)(k / a.C - 1) * 17 * a.B;
           if (live0) store_half<false>(ck + b0, a.B, s);
@@ -157,7 +184,10 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
       sum_v2 = add2(sum_v2, speed2);
     }
     if (k1 < a.H) {
-      // hand the group over to whoever picks up (seg+1, g)
+     if (!fell_back) {
+      // hand the group over to whoever picks up (seg+1, g).  A task that fell back does NOT publish: the slice
+      // record has one writer chain (seg 0 -> 1 -> ...), so a late predecessor can never overwrite a later
+      // hand-over; the successors of a fallen-back task time out in turn and roll forward themselves.
       float* sl = a.slice;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
@@ -176,6 +206,7 @@ sweep2_kernel(const __grid_constant__ DevConst P, const __grid_constant__ UnitNe
       __threadfence();
       __syncwarp();
       if (lane == 0) *(volatile int*)(a.flag + g) = seg + 1;
+     }
     } else {
       const float z0 = __ldg(a.x0 + 2), tdu = __ldg(a.thrust_du);
       const float J0 = rollout_cost_finish(a.cc, s.p[0].lo, s.p[1].lo, s.p[2].lo, z0, s.v[0].lo, s.v[1].lo,

@@ -60,6 +60,10 @@ extern "C" {
                                   * bits (different summation order), so it is opt-in: a sharded batch is bit-identical
                                   * to the whole one only while both run the same kernel. */
 
+#define AIRC_FLAG_PACKED 8u      /* rollout, 'nn' model: run the two-trajectories-per-thread kernel (the sweep's arithmetic)
+                                  * whatever the batch size; by default it serves batches of two waves and more, where it
+                                  * is the faster one.  A trajectory's bits do not depend on the batch under this flag. */
+
 /* Aircraft constants: AircraftConfiguration (utils.py:201-215), SixDOFOpts (base.py:9-14),
  * AircraftOpts (aircraft.py:22-38).  inertia / inertia_inv are about the shifted CoM
  * (aircraft.py:168-187, base.py:139-144) and are computed by the host side in float64. */
@@ -237,7 +241,7 @@ int airc_argmin(const AircHandle* h, const float* cost, int64_t B, float* out_mi
  *   w(k,c) = mix32(tkey + k*0x9E3779B9 + c*0x7F4A7C15)
  *   n(k,c) = byte0(w)+byte1(w)+byte2(w)+byte3(w) - 510          (integer in [-510,510], ~N(0,147.8^2))
  *   d_0    = s0_c*n(0,c);  d_k = fmaf(s_c, n(k,c), d_{k-1})     (FP32; s = (float)(sigma/147.80053))
- *   u_k[c] = min(max(U_nom[k][c] + d_k, lo_c), hi_c)
+ *   u_k[c] = min(max(U_nom[k][c] + d_k, lo_c), hi_c)        (a NaN in U_nom stays NaN)
  * oracle/cpu_ref.cpp restates the same generator, so every sampled sequence can be regenerated
  * bit-identically on the host. */
 typedef struct AircSweepParams {

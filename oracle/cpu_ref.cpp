@@ -250,7 +250,7 @@ struct SweepGen {
       const float n = (float)((int)((w & 255U) + ((w >> 8) & 255U) + ((w >> 16) & 255U) + (w >> 24)) - 510);
       d[c] = (k == 0) ? s0[c] * n : fmaf(s[c], n, d[c]);
       const float t = unom_k[chan[c]] + d[c];
-      u[chan[c]] = fminf(fmaxf(t, lo[c]), hi[c]);
+      u[chan[c]] = (t != t) ? t : fminf(fmaxf(t, lo[c]), hi[c]);   // NaN in the nominal sequence stays NaN
     }
   }
 };

@@ -1,5 +1,5 @@
-"""A/B of the rollout kernels (AIRC_ROLLOUT_IMPL=1 scalar, 2 packed): timing on the config-4 shard
-and a quick parity number against the float64 CPU reference.  Run once per variant."""
+"""A/B of the rollout kernels (default dispatch vs AIRC_FLAG_PACKED: `python profiles/ab_rollout.py [packed]`): timing on
+the config-4 shard and a quick parity number against the float64 CPU reference."""
 import os, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -13,12 +13,13 @@ from oracle.cpu_ref import CpuRef
 dev = torch.device("cuda:0")
 ac = Aircraft.from_problem(com=TRIM_COM, device=0, physical_integration_substeps=1, normalise=True)
 ref = CpuRef(make_params(AircraftConfiguration.from_json(), com=TRIM_COM), load_nn_blob())
-tag = os.environ.get("AIRC_ROLLOUT_IMPL", "default")
+PACKED = len(sys.argv) > 1 and sys.argv[1] == "packed"
+tag = "packed" if PACKED else "default"
 # parity: 2048 random states, 30 teacher-forced... free-running steps vs float64
 n, H = 2049, 30
 x0 = make_states(n, seed=77); U = make_control_sequences(n, H, seed=77)
 X = ac.rollout(torch.tensor(x0, dtype=torch.float32, device=dev), torch.tensor(U, dtype=torch.float32, device=dev),
-               0.01, return_trajectory=True, cost=True)
+               0.01, return_trajectory=True, cost=True, packed=PACKED)
 Xr = ref.rollout(x0, U, 0.01, normalise=True)
 cr = ref.rollout_cost(x0, U, 0.01, make_cost_params(), normalise=True)
 got = X.trajectory.double().cpu().numpy()
@@ -41,5 +42,5 @@ for B in (125000, 151552, 75776, 4096):
     Un = torch.zeros((H, 7), dtype=torch.float32, device=dev)
     U = ac.sweep_controls(Un, make_sweep_params(seed=1), 0, B, layout="soa")
     xs = torch.tensor(make_states(1, seed=4, level=True)[0], dtype=torch.float32, device=dev).view(13, 1).expand(13, B).contiguous()
-    ms = timeit(lambda: ac.rollout(xs, U, 0.01, layout="soa", cost=True, return_final=False))
+    ms = timeit(lambda: ac.rollout(xs, U, 0.01, layout="soa", cost=True, return_final=False, packed=PACKED))
     print(f"[{tag}] rollout B={B}: {ms:.4f} ms  {B*H/ms/1e6:.3f}e9 steps/s  {B*H*3953/ms/1e9:.2f} TFLOP/s", flush=True)

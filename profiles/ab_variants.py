@@ -36,6 +36,18 @@ if len(sys.argv) > 2 and sys.argv[2] == "lin":
     ms3 = time_launches(torch, lambda: ac.linearize(xa, ua, 0.01, want_dt=True), 10, 3)
     print("lin n=%%d soa %%.4f ms %%.3e evals/s %%.0f GB/s | aos %%.4f ms %%.3e evals/s | aos+dt %%.4f ms | checksum %%.6e" %% (n, ms, n/ms*1e3, n*1172/ms*1e3/1e9, ms2, n/ms2*1e3, ms3, cs))
     sys.exit(0)
+if len(sys.argv) > 2 and sys.argv[2] == "sweep":
+    from aircraft_b200.params import make_sweep_params
+    xs = torch.tensor(make_states(1, seed=4, level=True)[0], dtype=torch.float32, device=dev)
+    Un = torch.zeros((200, 7), dtype=torch.float32, device=dev)
+    sp = make_sweep_params(seed=1)
+    r = ac.sweep(xs, Un, 0.01, B, sampler=sp); ws = r.workspace
+    best = 1e9
+    for rep in range(3):
+        ms = time_launches(torch, lambda: ac.sweep(xs, Un, 0.01, B, sampler=sp, workspace=ws), 20, 3)
+        best = min(best, ms)
+    print("sweep %%.4f ms (best of 3 x 20)  %%.3e steps/s  %%.2f TFLOP/s  min cost %%.6e" %% (best, B*200/best*1e3, B*200*3953/best*1e3/1e12, float(r.min_cost)))
+    sys.exit(0)
 x0 = torch.tensor(make_states(1, seed=4, level=True).T, dtype=torch.float32, device=dev).expand(13, B).contiguous()
 U = device_control_sequences(torch, B, 200, seed=100, device=dev)
 ms = time_launches(torch, lambda: ac.rollout(x0, U, 0.01, layout="soa", return_final=False, cost=True), 10, 3)

@@ -1,3 +1,5 @@
+"""Times airc_sweep for the given batch sizes: python profiles/time_sweep2.py 125000,1000000
+(segment-count experiments are build variants: -DAIRC_AB_SWEEP_SEGMENTS=n, profiles/build_variants.py)."""
 import sys, os
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
@@ -21,4 +23,4 @@ for B in [int(b) for b in sys.argv[1].split(",")]:
     sp = make_sweep_params(seed=1)
     r = ac.sweep(x0, Un, 0.01, B, sampler=sp); ws = r.workspace
     ms = timeit(lambda: ac.sweep(x0, Un, 0.01, B, sampler=sp, workspace=ws))
-    print(f"S={os.environ.get('AIRC_SWEEP_SEGMENTS','auto')} B={B}: {ms:.4f} ms {B*200/ms/1e6:.3f}e9 steps/s", flush=True)
+    print(f"B={B}: {ms:.4f} ms {B*200/ms/1e6:.3f}e9 steps/s", flush=True)

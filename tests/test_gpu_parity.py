@@ -238,3 +238,47 @@ def test_cooperative_small_batch_rollout(ac, orc):
         d = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True, cost=True)
         assert col_err(a.trajectory.cpu(), d.trajectory.cpu().numpy(), batch_axes=(0, 1)) < 2e-5
         assert col_err(a.cost.cpu()[:, None], d.cost.cpu().numpy()[:, None]) < 1e-5
+
+
+@pytest.mark.parametrize("kind", ["default", "packed", "cooperative"])
+def test_nan_in_any_input_reaches_the_outputs(ac, kind):
+    """A NaN command or state must come out as NaN (the reference's tanh / CasADi arithmetic propagates it and its
+    callers test for it, main/dynamics/dynamics.py:108): every control the dynamics read (aileron, elevator, rudder,
+    flaps) and every state component reaches f, Phi, the rollout's final state and its cost; thrust (inert in the
+    dynamics, aircraft.py:320) reaches the cost through the increment penalty; p reaches p+ only.  A NaN cost sorts
+    last in the arg-min."""
+    n, H = 20, 6
+    x, u = make_states(n, seed=91), make_controls(n, seed=91)
+    U = make_control_sequences(n, H, seed=91)
+    kw = {"packed": True} if kind == "packed" else ({"cooperative": True} if kind == "cooperative" else {})
+    clean = ac.rollout(f32(x), f32(U), 0.01, cost=True, **kw)
+    assert torch.isfinite(clean.cost).all()
+    xb, ub, Ub = x.copy(), u.copy(), U.copy()
+    for j in range(13):
+        xb[j, j] = np.nan                    # node j: state component j
+    for j in range(7):
+        ub[13 + j, j] = np.nan               # node 13 + j: control j
+        Ub[13 + j, 2, j] = np.nan
+    f = ac.state_derivative(f32(xb.T), f32(ub.T)).T
+    phi = ac.state_update(f32(xb.T), f32(ub.T), 0.01).T
+    for j in range(3, 13):
+        assert torch.isnan(f[j]).any() and torch.isnan(phi[j]).any(), j
+    for j in range(3):
+        assert torch.isnan(phi[j, j]) and torch.isfinite(f[j]).all()
+    for j in (0, 1, 2, 6):
+        assert torch.isnan(f[13 + j]).any() and torch.isnan(phi[13 + j]).any(), j
+    for j in (3, 4, 5):
+        assert torch.isfinite(f[13 + j]).all()
+    r = ac.rollout(f32(xb), f32(Ub), 0.01, cost=True, **kw)
+    bad = torch.isnan(r.cost)
+    assert bad[:13].all() and bad[13:20].all(), bad
+    for j in (0, 1, 2, 6):
+        assert torch.isnan(r.final[13 + j]).any()
+    _, Ab, _ = ac.linearize(f32(xb), f32(ub), 0.01)
+    assert torch.isnan(Ab[3:13]).flatten(1).any(dim=1).all()
+    # arg-min: NaN costs sort last
+    c = clean.cost.clone()
+    c[int(c.argmin())] = float("nan")
+    m, i = ac.argmin(c)
+    ref = torch.where(torch.isnan(c), torch.full_like(c, float("inf")), c)
+    assert int(i) == int(ref.argmin()) and torch.isfinite(m).all()

@@ -189,19 +189,23 @@ def test_full_size_shard_properties(ac, x0):
 
 
 # ---------------------------------------------------------------- packed (two-trajectory) rollout kernel
+class _Packed:
+    """The aircraft with explicit-control rollouts on the packed kernel (AIRC_FLAG_PACKED; by default it is chosen
+    for batches of >= 2 waves only)."""
+
+    def __init__(self, ac):
+        self._ac = ac
+
+    def rollout(self, *a, **kw):
+        return self._ac.rollout(*a, packed=True, **kw)
+
+    def __getattr__(self, name):
+        return getattr(self._ac, name)
+
+
 @pytest.fixture(scope="module")
-def ac_packed(built):
-    """A handle whose explicit-control rollouts are forced onto the packed kernel (by default it is
-    chosen for batches of >= 2 waves only)."""
-    import os
-    from aircraft_b200 import Aircraft
-    os.environ["AIRC_ROLLOUT_IMPL"] = "2"
-    try:
-        a = Aircraft.from_problem(com=TRIM_COM, device=DEV, physical_integration_substeps=1, normalise=True)
-        a.handle          # airc_create reads the knob
-    finally:
-        del os.environ["AIRC_ROLLOUT_IMPL"]
-    return a
+def ac_packed(ac):
+    return _Packed(ac)
 
 
 def test_packed_rollout_parity_and_lane_independence(ac_packed, ac, ref):
@@ -244,3 +248,15 @@ def test_sweep_equals_packed_explicit_rollout(ac_packed, x0):
     assert (r.cost - e.cost).abs().max().item() <= 2e-6 * e.cost.abs().max().item()
     am = int(r.argmin.item())
     assert torch.equal(e.trajectory[:, :, am], r.trajectory)
+
+
+def test_nan_in_the_nominal_sequence_propagates(ac, x0):
+    """The sampler's clamp keeps NaN (min.NaN / max.NaN): a NaN in U_nom makes every candidate's cost NaN instead of
+    silently sampling around the lower actuator limit."""
+    B, H = 300, 12
+    Un = nominal(H)
+    Un[5, 1] = np.nan
+    r = ac.sweep(f32(x0), f32(Un), DT, B, sampler=make_sweep_params(seed=4), return_costs=True)
+    assert torch.isnan(r.cost).all()
+    U = ac.sweep_controls(f32(Un), make_sweep_params(seed=4), 0, 8)
+    assert torch.isnan(U[:, 5, 1]).all() and torch.isfinite(U[:, :5]).all()

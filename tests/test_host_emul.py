@@ -154,3 +154,20 @@ def test_linearize_tile_with_stall_scaling(built):
     xo, Ao, Bo = orc.linearize(t64(x), t64(u), 0.01)
     assert col_err(A, Ao.numpy(), atol=1e-3) < PARITY_TOL
     assert col_err(B, Bo.numpy(), atol=1e-3) < PARITY_TOL
+
+
+def test_nan_reaches_f_and_phi(built):
+    """The NaN-preserving clamp of the logistic (min_nan): a NaN aileron / elevator / state must not be turned into
+    a saturated hidden layer and finite coefficients."""
+    p, blob = params_for()
+    emu = HostEmul(p, blob)
+    x, u = make_states(20, seed=92), make_controls(20, seed=92)
+    for j in range(3, 13):
+        x[j, j] = np.nan
+    for k, j in enumerate((0, 1, 2, 6)):
+        u[13 + k, j] = np.nan
+    f = emu.state_derivative(x, u)
+    phi = emu.state_update(x, u, 0.01, 1, False)
+    for j in list(range(3, 13)) + [13, 14, 15, 16]:
+        assert np.isnan(f[j]).any() and np.isnan(phi[j]).any(), j
+    assert np.isfinite(f[:3]).all() and np.isfinite(f[17:]).all()
