@@ -4,7 +4,9 @@ RK4, plus dPhi/dx and dPhi/du.  CUDA only; there is no CPU fallback."""
 from .config import (AircraftConfiguration, AircraftOpts, SixDOFOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH, NETWORKPATH, DATAPATH, TRIM_COM)
 
-__version__ = "0.1.0"
+from .dm import DM
+
+__version__ = "0.2.0"
 
 
 def __getattr__(name):  # lazy: the CUDA library is loaded on first use of the compute path

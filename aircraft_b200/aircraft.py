@@ -29,6 +29,7 @@ from . import _cabi
 from ._cabi import (FLAG_COOPERATIVE, FLAG_NORMALISE, FLAG_PACKED, FLAG_SHARED_U, LAYOUT_AOS, LAYOUT_SOA, NU, NX, NZ)
 from .config import (AircraftConfiguration, AircraftOpts, DEFAULT_MODEL_PATH,
                      DEFAULT_PROBLEM_PATH)
+from .dm import DM, Function, as_dm, as_dm_tensor
 from .params import (load_linear_model, load_nn_blob, load_poly_model, make_cost_params, make_params,
                      make_sweep_params)
 
@@ -192,9 +193,11 @@ class Aircraft:
 
     Differences a caller can see, all forced by the hardware path:
       * arithmetic is FP32 on the GPU (results match the float64 reference to ~1e-6 per step);
-      * ``state_update`` / ``state_derivative`` are plain callables (no CasADi graph), so they
-        cannot be embedded symbolically into ``ca.Opti``; the Jacobians IPOPT would derive are
-        served by :meth:`linearize` instead;
+      * ``state_update`` / ``state_derivative`` are plain callables (no CasADi graph); they return
+        DM-compatible arrays (``.full()``, ``.toarray()``: dm.py), so the reference's numeric call sites run
+        unmodified.  Symbolic embedding into ``ca.Opti`` goes through ``casadi_adapter.py`` (a
+        ``casadi.Callback`` over the C ABI: eval, Jacobian blocks, Lagrangian-Hessian blocks) where CasADi is
+        installed; the same blocks are served directly by :meth:`linearize` / :meth:`lagrangian_hessian`;
       * ``com`` and ``normalise`` may be assigned after construction exactly as the reference's
         scripts do; the constant block is rebuilt on the next call.
     """
@@ -383,7 +386,7 @@ class Aircraft:
             return 0.0, d.to(device=f"cuda:{self._device}", dtype=torch.float32).contiguous()
         return 0.0, self._host32(d, "dt")
 
-    def state_derivative(self, x, u):
+    def _state_derivative(self, x, u):
         """f(x,u): the reference's ca.Function 'dynamics' (base.py:402-406)."""
         x2, u2, n, squeeze = self._columns(x, u)
         lib, h = self._lib, self.handle
@@ -392,6 +395,7 @@ class Aircraft:
             out = torch.empty((NX, n), dtype=torch.float32, device=xd.device)
             _check(lib.airc_state_derivative(h, xd.data_ptr(), ud.data_ptr(), n, LAYOUT_SOA,
                                              out.data_ptr(), self._stream()), lib, "airc_state_derivative")
+            out = as_dm_tensor(out)
         else:
             xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
             out = np.empty((NX, n), np.float32)
@@ -400,8 +404,8 @@ class Aircraft:
             out = self._like(out, x)
         return out[:, 0] if squeeze else out
 
-    def state_update(self, x, u, dt, *, substeps: Optional[int] = None,
-                     normalise: Optional[bool] = None):
+    def _state_update(self, x, u, dt, *, substeps: Optional[int] = None,
+                      normalise: Optional[bool] = None):
         """Phi(x,u,dt): the reference's ca.Function 'state_update' (base.py:476-480).
         n = physical_integration_substeps RK4 steps of dt/n; quaternion normalised once at the end
         when ``normalise`` (base.py:466-474)."""
@@ -416,6 +420,7 @@ class Aircraft:
             _check(lib.airc_state_update(h, xd.data_ptr(), ud.data_ptr(), dts, self._ptr(dtn), n, ns,
                                          fl, LAYOUT_SOA, out.data_ptr(), self._stream()),
                    lib, "airc_state_update")
+            out = as_dm_tensor(out)
         else:
             xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
             out = np.empty((NX, n), np.float32)
@@ -427,15 +432,16 @@ class Aircraft:
 
     @staticmethod
     def _like(out: np.ndarray, ref):
-        """Host results come back in the caller's container and float dtype (the reference hands
-        back float64 DM values; FP32 results are widened, not recomputed)."""
+        """Host results come back in the caller's float dtype as a DM-compatible numpy array (dm.py: the
+        reference hands back float64 casadi.DM values and its call sites use .full() / .toarray() on them;
+        FP32 results are widened, not recomputed)."""
         if _is_torch(ref):
             t = torch.from_numpy(out)
             return t.to(ref.dtype) if ref.dtype.is_floating_point else t
         dt = getattr(ref, "dtype", None)
         if dt is not None and np.issubdtype(dt, np.floating):
-            return out.astype(dt, copy=False)
-        return out.astype(np.float64)
+            return as_dm(out.astype(dt, copy=False))
+        return as_dm(out.astype(np.float64))
 
     # ------------------------------------------------------------------ batched-native entry points
     def rollout(self, x0, U, dt: float, *, substeps: Optional[int] = None,
@@ -687,6 +693,7 @@ class Aircraft:
             out = torch.empty((_cabi.NDIAG, n), dtype=torch.float32, device=xd.device)
             _check(lib.airc_diagnostics(h, xd.data_ptr(), ud.data_ptr(), n, LAYOUT_SOA, out.data_ptr(),
                                         self._stream()), lib, "airc_diagnostics")
+            out = as_dm_tensor(out)
         else:
             xh, uh = self._host32(x2, "x"), self._host32(u2, "u")
             out = np.empty((_cabi.NDIAG, n), np.float32)
@@ -707,38 +714,42 @@ class Aircraft:
                 np.zeros((NU,) if n is None else (NU, n))
         return self.diagnostics(x, u)[name]
 
-    def v_frd_rel(self, x, u):
-        return self._diag("v_frd_rel", x, u)
+    # The reference exposes all of these as PROPERTIES that return a ca.Function (base.py:147-241,385-480;
+    # aircraft.py:255-330): `aircraft.state_update(x, u, dt)` calls the returned function and
+    # `aircraft.state_update.size1_in(0)` introspects it.  Same here (dm.Function over the CUDA entry points).
+    _FUNCTIONS = {
+        # attribute: (Function name, inputs, input sizes, output name, output size)
+        "state_update": ("state_update", ("x", "u", "dt"), (NX, NU, 1), "x_next", NX),
+        "state_derivative": ("dynamics", ("x", "u"), (NX, NU), "x_dot", NX),
+        "v_frd_rel": ("v_frd_rel", ("x", "u"), (NX, NU), "v_frd_rel", 3),
+        "airspeed": ("airspeed", ("x", "u"), (NX, NU), "airspeed", 1),
+        "alpha": ("alpha", ("x", "u"), (NX, NU), "alpha", 1),
+        "beta": ("beta", ("x", "u"), (NX, NU), "beta", 1),
+        "qbar": ("qbar", ("x", "u"), (NX, NU), "qbar", 1),
+        "coefficients": ("coefficients", ("x", "u"), (NX, NU), "coefficients", 6),
+        "forces_frd": ("forces_frd", ("x", "u"), (NX, NU), "forces_frd", 3),
+        "moments_frd": ("moments_frd", ("x", "u"), (NX, NU), "moments_frd", 3),
+        "phi": ("phi", ("x",), (NX,), "phi", 1),
+        "theta": ("theta", ("x",), (NX,), "theta", 1),
+        "psi": ("psi", ("x",), (NX,), "psi", 1),
+    }
 
-    def airspeed(self, x, u):
-        return self._diag("airspeed", x, u)
-
-    def alpha(self, x, u):
-        return self._diag("alpha", x, u)
-
-    def beta(self, x, u):
-        return self._diag("beta", x, u)
-
-    def qbar(self, x, u):
-        return self._diag("qbar", x, u)
-
-    def coefficients(self, x, u):
-        return self._diag("coefficients", x, u)
-
-    def forces_frd(self, x, u):
-        return self._diag("forces_frd", x, u)
-
-    def moments_frd(self, x, u):
-        return self._diag("moments_frd", x, u)
-
-    def phi(self, x):
-        return self._diag("phi", x)
-
-    def theta(self, x):
-        return self._diag("theta", x)
-
-    def psi(self, x):
-        return self._diag("psi", x)
+    def __getattr__(self, attr):
+        spec = Aircraft._FUNCTIONS.get(attr)
+        if spec is None:
+            raise AttributeError(attr)
+        name, ins, sizes, out, osize = spec
+        if attr == "state_update":
+            fn = self._state_update
+        elif attr == "state_derivative":
+            fn = self._state_derivative
+        elif len(ins) == 1:
+            fn = (lambda x, _a=attr: self._diag(_a, x))
+        else:
+            fn = (lambda x, u, _a=attr: self._diag(_a, x, u))
+        f = Function(name, fn, ins, sizes, (out,), (osize,))
+        self.__dict__[attr] = f           # cached: later look-ups do not come through __getattr__
+        return f
 
     # ------------------------------------------------------------------ sampling-MPC sweep
     def sweep(self, x0, U_nom, dt: float, B: int, *, sampler=None, cost=True,

@@ -54,6 +54,18 @@ def global_argmin(local_min: torch.Tensor, local_global_idx: torch.Tensor,
     return mins[best][0], int(keys[best, 1]), best
 
 
+def local_min_or_sentinel(aircraft, cost_local: torch.Tensor, start: int):
+    """(min, GLOBAL arg-min) of this rank's costs for the exchange.  A rank whose shard is empty (total < world)
+    contributes a sentinel that can never win -- NaN sorts last and the index is beyond any real one -- instead of
+    calling the arg-min kernel with B = 0 (AIRC_EINVAL) and leaving the other ranks blocked in the all-gather."""
+    if cost_local.numel() == 0:
+        dev = cost_local.device
+        return (torch.full((1,), float("nan"), dtype=torch.float32, device=dev),
+                torch.full((1,), 2 ** 62, dtype=torch.int64, device=dev))
+    lmin, lidx = aircraft.argmin(cost_local)
+    return lmin, lidx + start
+
+
 @dataclass
 class SweepResult:
     min_cost: Any                    # 0-dim tensor (no host sync is forced)
@@ -97,8 +109,8 @@ class ShardedRollout:
         exchange, and the winner's trajectory on every rank."""
         ac = self.aircraft
         start, stop = self.local_range(total)
-        lmin, lidx = ac.argmin(cost_local)
-        gmin, gidx, owner = global_argmin(lmin, lidx + start, self.group)
+        lmin, lgidx = local_min_or_sentinel(ac, cost_local, start)
+        gmin, gidx, owner = global_argmin(lmin, lgidx, self.group)
         soa = layout == "soa"
         shared = U_local.ndim == 2
         H = U_local.shape[0] if (soa or shared) else U_local.shape[1]

@@ -15,6 +15,22 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (sm_100a); run on the B200 box")
 
 
+def pytest_collection_modifyitems(config, items):
+    """`pytest tests` on a box without a CUDA device: the gpu-marked tests are skipped (with the reason), not
+    failed; `-m gpu` on the B200 box runs them all."""
+    try:
+        import torch
+        have = torch.cuda.is_available()
+    except Exception:
+        have = False
+    if have:
+        return
+    skip = pytest.mark.skip(reason="needs a CUDA device (sm_100a); aircraft_b200 has no CPU path")
+    for it in items:
+        if "gpu" in it.keywords:
+            it.add_marker(skip)
+
+
 @pytest.fixture(scope="session")
 def built():
     """The in-tree CUDA library and the CPU checkers exist (build once per session)."""

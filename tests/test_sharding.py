@@ -7,7 +7,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from aircraft_b200.sharding import _orderable, gather_varlen, global_argmin, shard_range
+from aircraft_b200.sharding import _orderable, gather_varlen, global_argmin, local_min_or_sentinel, shard_range
 
 
 def test_shard_range_partitions():
@@ -73,3 +73,43 @@ def test_global_argmin_and_gather_gloo_world2():
         assert gidx == ref_idx and abs(gmin - ref_min) < 1e-7 and owner == 1
         assert gathered_ok
         assert tidx == 1 and towner == 0
+
+
+class _TorchArgmin:
+    """stands in for Aircraft.argmin (the kernel refuses B = 0, as airc_argmin does)"""
+
+    def argmin(self, cost):
+        assert cost.numel() > 0, "AIRC_EINVAL"
+        c = torch.where(torch.isnan(cost), torch.full_like(cost, float("inf")), cost)
+        return c.min().reshape(1), c.argmin().reshape(1)
+
+
+def _worker_empty(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        total = 1                                        # fewer rollouts than ranks: rank 1's shard is empty
+        cost = torch.tensor([3.25])
+        a, b = shard_range(total, rank, world)
+        lmin, lg = local_min_or_sentinel(_TorchArgmin(), cost[a:b], a)
+        gmin, gidx, owner = global_argmin(lmin, lg)
+        q.put((rank, b - a, float(gmin), gidx, owner))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_empty_shard_does_not_hang_or_win_gloo_world2():
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_empty, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert [r[1] for r in res] == [1, 0]
+    for _, _, gmin, gidx, owner in res:
+        assert gmin == 3.25 and gidx == 0 and owner == 0
