@@ -114,7 +114,8 @@ AIRC_D F2 f2_unpack(unsigned long long v) {
 // kernels (airc_packed.cuh) were tuned with -- ptxas then keeps the weights in uniform registers with the fewest
 // moves.  fma2b / add2b / mul2b are the CUDA 12.8+ builtins: identical arithmetic, but the front end handles
 // thousands of them per function in seconds where the same number of asm statements takes minutes, so the
-// surrogate-with-Jacobian and the tangent code (airc_dynamics.cuh, airc_jac.cuh, tfma vocabulary) use these.
+// surrogate-with-Jacobian (airc_dynamics.cuh, airc_coop.cuh: 16 unrolled unit pairs) uses these.  The tangent / jet
+// vocabulary below stays on the PTX spelling: with the builtins the jet kernels (airc_jet.cuh) spill six times more.
 AIRC_HD F2 fma2(const F2& a, const F2& b, const F2& c) {
 #if defined(__CUDA_ARCH__)
   unsigned long long d;
@@ -172,17 +173,17 @@ AIRC_HD F2 bc2(float a) { return F2{a, a}; }
 // forward-mode tangent code is written once.  Primal quantities stay scalar and enter packed
 // instructions as broadcast operands (free in SASS: "R.F32" operand form of FFMA2).
 AIRC_HD float tfma(float a, float b, float c) { return fmaf(a, b, c); }
-AIRC_HD F2 tfma(float a, const F2& b, const F2& c) { return fma2b(bc2(a), b, c); }
-AIRC_HD F2 tfma(const F2& a, float b, const F2& c) { return fma2b(a, bc2(b), c); }
-AIRC_HD F2 tfma(const F2& a, const F2& b, const F2& c) { return fma2b(a, b, c); }
+AIRC_HD F2 tfma(float a, const F2& b, const F2& c) { return fma2(bc2(a), b, c); }
+AIRC_HD F2 tfma(const F2& a, float b, const F2& c) { return fma2(a, bc2(b), c); }
+AIRC_HD F2 tfma(const F2& a, const F2& b, const F2& c) { return fma2(a, b, c); }
 AIRC_HD float tmul(float a, float b) { return a * b; }
-AIRC_HD F2 tmul(float a, const F2& b) { return mul2b(bc2(a), b); }
-AIRC_HD F2 tmul(const F2& a, float b) { return mul2b(a, bc2(b)); }
-AIRC_HD F2 tmul(const F2& a, const F2& b) { return mul2b(a, b); }
+AIRC_HD F2 tmul(float a, const F2& b) { return mul2(bc2(a), b); }
+AIRC_HD F2 tmul(const F2& a, float b) { return mul2(a, bc2(b)); }
+AIRC_HD F2 tmul(const F2& a, const F2& b) { return mul2(a, b); }
 AIRC_HD float tadd(float a, float b) { return a + b; }
-AIRC_HD F2 tadd(const F2& a, const F2& b) { return add2b(a, b); }
+AIRC_HD F2 tadd(const F2& a, const F2& b) { return add2(a, b); }
 AIRC_HD float tsub(float a, float b) { return a - b; }
-AIRC_HD F2 tsub(const F2& a, const F2& b) { return fma2b(bc2(-1.0f), b, a); }
+AIRC_HD F2 tsub(const F2& a, const F2& b) { return fma2(bc2(-1.0f), b, a); }
 template <class T> AIRC_HD T tzero();
 template <> AIRC_HD float tzero<float>() { return 0.0f; }
 template <> AIRC_HD F2 tzero<F2>() { return F2{0.0f, 0.0f}; }

@@ -3,29 +3,25 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference] [--workload c4|c2]
 
-Metric (BASELINE.json): surrogate-RK4 state-steps/s (+ Jacobian evals/s) at 1/2/4/8 B200 next to
-the CPU path on the box's host cores.
+Metric (BASELINE.json): surrogate-RK4 state-steps/s AND Jacobian evals/s at 1/2/4/8 B200 next to the CPU path on the
+box's host cores.  Everything the metric names is a compact TOP-LEVEL block of the one JSON line:
 
-A "step" is one pass of the hot path over one batch of synthetic input:
-  workload c4 (default, every N): the per-GPU shard of BASELINE config 4, the sampling-MPC sweep
-      "1M control-sequence rollouts x horizon 200 sharded over 8 B200" = 125 000 rollouts x 200
-      RK4 steps per GPU from one shared initial state.  The control sequences are SAMPLED IN THE
-      KERNEL around one nominal sequence (counter-based generator keyed on the global trajectory
-      index, include/aircraft_b200.h), rolled out with the fused loss, reduced to (min, arg-min) by
-      warp shuffles, and the winner's trajectory is reproduced from state checkpoints; for N>1
-      the per-rank winner records (16 kB) are all-gathered over NCCL and selected on the device.
-      Weak scaling: at N=8 the job is exactly config 4.  The kernel reads 5.7 kB per launch and
-      streams > 126 MB of checkpoints through L2, so nothing is cached between timed iterations.
-      The same shard with EXPLICIT control tensors (700 MB per GPU, PCIe-bound end to end) is
-      reported under "extra".c4_explicit.
-  workload c2: BASELINE config 2, 4096 rollouts x 200 from trim states on each GPU (a latency
-      case: 128 warps on 592 SM sub-partitions); always reported under "extra" at N=1.
-  Jacobians: BASELINE config 3 (65 536 x 100 nodes) and config 5's per-GPU shard (51 200 nodes),
-      reported under "jacobian" / "extra".
+  value / e2e / roofline   main line: the per-GPU shard of BASELINE config 4 (weak scaling) -- the sampling-MPC sweep
+        "1M control-sequence rollouts x horizon 200 sharded over 8 B200" = 125 000 rollouts x 200 RK4 steps per GPU
+        from one shared initial state; controls SAMPLED IN THE KERNEL around one nominal sequence, fused loss,
+        warp-shuffle arg-min, winner reproduced from checkpoints; N>1: all-gather of the 16 kB winner records +
+        device-side selection.  At N=8 the job is exactly config 4.  (c4 is the largest single-GPU state-step config
+        and the one the 1e10 target is quoted on; config 2 fits one GPU too and is reported under "c2".)
+  sustained                the same step back to back for >= 2 s with the clock sampler running (>= 10 samples)
+  config4_strong           config 4 as BASELINE words it: 1 000 000 rollouts TOTAL over N GPUs (strong scaling)
+  c2                       BASELINE config 2: 4096 rollouts x 200 from trim states on ONE GPU (rank 0), latency case
+  jacobian                 Jacobian evals/s aggregated over the N ranks (max time over ranks): BASELINE config 3
+        (65 536 x 100 nodes PER GPU, weak) with roofline in GB/s and executed FLOP/s, BASELINE config 5 exactly
+        (8192 windows x 50 nodes TOTAL over N GPUs), e2e through airc_linearize_host (pinned host buffers), CPU baseline
+  extra                    config 1, explicit-control shard, Hessian blocks, the reference's 298-node MPC blocks
 
-`--impl reference` times the CPU restatement of the reference path (oracle/cpu_ref.cpp, float64,
-OpenMP over all host cores; the reference's own CasADi evaluation cannot run on this box) on the
-same workload, each step a bounded sample of it.
+`--impl reference` times the CPU restatement of the reference path (oracle/cpu_ref.cpp, float64, OpenMP over all host
+cores; the reference's own CasADi evaluation cannot run on this box) on the same workload, each step a bounded sample.
 """
 from __future__ import annotations
 
@@ -310,12 +306,26 @@ def run_native(args):
     else:
         line = run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, windows, barrier)
 
-    # ---- side measurements on rank 0 / every rank (no collectives inside)
-    extra = {}
+    peak = line["roofline"]["peak"]
+
+    def rank_max(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     if not args.no_extras:
-        extra.update(side_measurements(torch, ac, dev, rank, args))
-        if "c3" in extra:
-            line["jacobian"] = extra.pop("c3")
+        # ---- BASELINE config 2 (one GPU): rank 0 measures, the others wait
+        if rank == 0 and args.workload != "c2":
+            line["c2"] = measure_c2(torch, ac, dev, peak, max(5, min(K, 20)))
+        barrier()
+        # ---- Jacobian evals/s over all ranks: config 3 per GPU (weak), config 5 exactly (strong), e2e
+        line["jacobian"] = measure_jacobian(torch, ac, dev, rank, world, max(5, min(K, 20)), peak, rank_max, barrier,
+                                            clocks, windows)
+        barrier()
+        if rank == 0:
+            line["extra"] = side_extras(torch, ac, dev, args)
     if rank == 0 and world == 1:
         ref = _cpu_ref()
         rate, n, sec = cpu_rollout_rate(ref, args.cpu_seconds)
@@ -326,9 +336,7 @@ def run_native(args):
         if "jacobian" in line:
             jr, jn, js = cpu_jacobian_rate(ref, 4.0)
             line["jacobian"]["cpu_baseline"] = {"value": jr, "unit": "jacobian-evals/s", "cores": ref.threads,
-                                                "kind": "port", "sample": f"{jn} nodes ({js:.1f} s)"}
-    if extra:
-        line["extra"] = extra
+                                                "kind": "port", "sample": f"{jn} nodes ({js:.1f} s), 20-direction forward mode"}
     if rank == 0:
         clocks.stop()
         line["clocks"] = clocks.summary(windows)
@@ -346,38 +354,45 @@ def fp32_peak(ac):
     return float(tf.value)
 
 
-def ncu_traffic(kernel: str):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full`
-    capture of this workload (profiles/r*_ncu_summary_sweep2.txt, latest); None when the summary is not there."""
-    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+def csrc_sha():
+    import hashlib
+    h = hashlib.sha256()
+    for p in sorted((ROOT / "aircraft_b200" / "csrc").glob("*")):
+        h.update(p.name.encode())
+        h.update(p.read_bytes())
+    return h.hexdigest()[:16]
+
+
+def kernel_audit(name: str):
+    """One entry of profiles/r2_kernel_audit.json (written by profiles/ncu_audit.py from an `ncu --set full` capture
+    of this workload): DRAM bytes and EXECUTED FP32 flops per launch of the kernel.  ncu cannot run inside the bench,
+    so the entry carries the hash of the CUDA sources it was captured on and is reported as stale when they changed."""
     try:
-        rd = wr = None
-        hit = False
-        cands = sorted((ROOT / "profiles").glob("r*_ncu_summary_sweep2.txt"))      # the latest committed capture
-        for ln in cands[-1].read_text().splitlines():
-            t = ln.split()
-            if ln.startswith("Kernel Name"):
-                hit = kernel in ln
-            elif hit and t and t[0] == "dram__bytes_read.sum" and rd is None:
-                rd = float(t[1].replace(",", "")) * unit[t[2]]
-            elif hit and t and t[0] == "dram__bytes_write.sum" and wr is None:
-                wr = float(t[1].replace(",", "")) * unit[t[2]]
-        return None if rd is None or wr is None else rd + wr
+        e = json.loads((ROOT / "profiles" / "r2_kernel_audit.json").read_text())[name]
+        e = dict(e)
+        e["stale"] = e.get("csrc_sha") != csrc_sha()
+        return e
     except Exception:
         return None
 
 
-def rollout_roofline(kernel, tflops, peak, steps_per_launch, ms_kernel, ms_step, note="", traffic=None):
-    return {"kernel": kernel, "bound": "fp32", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
-            "frac": tflops / peak,
-            "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); "
-                           "MEASURED_PEAKS.json has no FP32 CUDA-core entry",
-            "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": tflops / FP32_NOMINAL_TFLOPS,
-            "flops_per_state_step": F_STEP, "state_steps_per_launch": steps_per_launch,
-            "kernel_ms": ms_kernel, "kernel_share_of_step": ms_kernel / ms_step, "traffic": traffic,
-            "traffic_unit": "bytes of DRAM read + write per launch (ncu --set full capture under profiles/); "
-                            "the kernel is FP32-bound, the traffic is the checkpoint / slice records",
-            "note": note}
+def rollout_roofline(kernel, tflops, peak, steps_per_launch, ms_kernel, ms_step, note="", audit=None):
+    r = {"kernel": kernel, "bound": "fp32", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+         "frac": tflops / peak,
+         "peak_source": "FFMA probe measured in this run (airc_measure_fp32_peak); MEASURED_PEAKS.json has no FP32 "
+                        "CUDA-core entry",
+         "peak_nominal": FP32_NOMINAL_TFLOPS, "frac_of_nominal": tflops / FP32_NOMINAL_TFLOPS,
+         "flops_per_state_step": F_STEP, "state_steps_per_launch": steps_per_launch,
+         "kernel_ms": ms_kernel, "kernel_share_of_step": ms_kernel / ms_step, "traffic": None, "note": note}
+    if audit and abs(audit["units_per_launch"] - steps_per_launch) < 0.5:
+        ex = audit["executed_fp32_flops_per_unit"]
+        r.update({"traffic": audit["dram_bytes_per_launch"],
+                  "traffic_source": f"profiles/{audit['capture']} via profiles/r2_kernel_audit.json (ncu --set full of this "
+                                    f"workload; CUDA sources {'CHANGED since' if audit['stale'] else 'unchanged since'} "
+                                    f"the capture); the kernel is FP32-bound, the traffic is checkpoint / slice records",
+                  "executed_flops_per_state_step": ex,
+                  "achieved_executed": tflops * ex / F_STEP, "frac_executed": tflops * ex / F_STEP / peak})
+    return r
 
 
 def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, windows, barrier):
@@ -466,11 +481,73 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
         el = float(t.item())
     e2e_value = total * H * Ke / el
 
+    # ---- sustained: the same step back to back for >= 2 s of device time, clock sampler running
+    n_sus = int(max(50, min(4000, 2200.0 / ms_step)))
+    barrier()
+    t_mark = clocks.mark()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(n_sus):
+        step(False)
+    s1.record()
+    barrier()
+    sus_window = (t_mark, clocks.mark())
+    windows.append(sus_window)
+    ms_sus = s0.elapsed_time(s1)
+    if world > 1:
+        t = torch.tensor([ms_sus], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_sus = float(t.item())
+    sustained = {"launches": n_sus, "seconds": ms_sus * 1e-3, "ms_per_step": ms_sus / n_sus,
+                 "value": total * H / (ms_sus / n_sus * 1e-3), "unit": "state-steps/s",
+                 "tflops_per_gpu": per_gpu * H * F_STEP / (ms_sus / n_sus * 1e-3) / 1e12,
+                 "frac_of_fp32_peak": per_gpu * H * F_STEP / (ms_sus / n_sus * 1e-3) / 1e12 / peak,
+                 "clocks": clocks.summary([sus_window]) if rank == 0 else None}
+
+    # ---- config 4 as BASELINE words it: 1 000 000 rollouts in total over the N GPUs (strong scaling)
+    strong = None
+    if (per_gpu, H) == (C4_TOTAL // C4_GPUS, H_ROLL):
+        ws_s = None
+
+        def sstep():
+            nonlocal ws_s
+            if world > 1:
+                o = sweep_sampled(ac, x0_d, Un_d, DT, C4_TOTAL, sampler=sp, cost=cp, workspace=ws_s)
+            else:
+                o = ac.sweep(x0_d, Un_d, DT, C4_TOTAL, sampler=sp, cost=cp, workspace=ws_s)
+            ws_s = o.workspace
+            return o
+
+        for _ in range(2):
+            so = sstep()
+        barrier()
+        Ks = max(5, min(K, 10))
+        q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        q0.record()
+        for _ in range(Ks):
+            so = sstep()
+        q1.record()
+        barrier()
+        ms_s = q0.elapsed_time(q1)
+        if world > 1:
+            t = torch.tensor([ms_s], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms_s = float(t.item())
+        ms_s /= Ks
+        strong = {"workload": f"BASELINE config 4 exactly: {C4_TOTAL} rollouts x {H} in total, {C4_TOTAL // world} per GPU",
+                  "scaling": "strong", "n_gpus": world, "steps": Ks, "ms_per_step": ms_s,
+                  "value": C4_TOTAL * H / (ms_s * 1e-3), "unit": "state-steps/s",
+                  "tflops_per_gpu": C4_TOTAL / world * H * F_STEP / (ms_s * 1e-3) / 1e12,
+                  "frac_of_fp32_peak": C4_TOTAL / world * H * F_STEP / (ms_s * 1e-3) / 1e12 / peak,
+                  "best": {"min_cost": float(so.min_cost), "argmin": int(so.argmin)}}
+        del ws_s
+
     return {
         "metric": "surrogate RK4 state-steps/s", "value": value, "unit": "state-steps/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config("c4", per_gpu, world),
+        "sustained": sustained, "config4_strong": strong,
         "e2e": {"value": e2e_value, "unit": "state-steps/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": Ke,
                 "path": "airc_sweep_host (C ABI, host buffers in, winner record out)" if world == 1 else
@@ -480,7 +557,7 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
         "roofline": rollout_roofline("sweep2_kernel<ckpt> (+ sweep2_prep, sweep_winner2: < 2 % of the call)",
                                      roll_tflops, peak, per_gpu * H, ms_roll, ms_step,
                                      "kernel_ms = CUDA events around the airc_sweep call (three launches)",
-                                     traffic=ncu_traffic("sweep2_kernel") if (per_gpu, H) == (C4_TOTAL // C4_GPUS, H_ROLL) else None),
+                                     audit=kernel_audit("sweep2")),
     }
 
 
@@ -532,11 +609,112 @@ def measured_peaks():
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback (B200_PROFILING.md)"
 
 
-def side_measurements(torch, ac, dev, rank, args):
-    """The other BASELINE configs, device-timed with CUDA events (per GPU; no collectives)."""
-    from aircraft_b200.workloads import make_controls, make_states, trim_states
-    out = {}
+def measure_c2(torch, ac, dev, peak, K):
+    """BASELINE config 2 -- 4096 rollouts x horizon 200 from random trim states on ONE GPU, explicit controls, fused
+    cost: the latency case (4096 trajectories cannot fill 148 SMs with one trajectory per thread)."""
+    from aircraft_b200.workloads import trim_states
+    xs, _ = trim_states(ac, 4096, seed=0)
+    x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
+    U = device_control_sequences(torch, 4096, H_ROLL, seed=200, device=dev)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)   # 256 MB > 126 MB L2
+    ms_default = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True), K, 3, flush)
+    ms_lat = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True, cooperative=True), K, 3, flush)
+    ms = min(ms_default, ms_lat)
+    tfl = 4096 * H_ROLL * F_STEP / (ms * 1e-3) / 1e12
+    return {"workload": "BASELINE config 2: 4096 rollouts x horizon 200 from trim states, 1 GPU, U[H,7,B] explicit, fused cost",
+            "ms_per_launch": ms, "value": 4096 * H_ROLL / (ms * 1e-3), "unit": "state-steps/s",
+            "kernel": "latency mode (AIRC_FLAG_COOPERATIVE)" if ms_lat <= ms_default else "default dispatch",
+            "ms_default_dispatch": ms_default, "ms_latency_mode": ms_lat,
+            "roofline": {"bound": "fp32 (latency-bound: 4096 trajectories on 148 SMs)", "achieved": tfl, "peak": peak,
+                         "unit": "TFLOP/s", "frac": tfl / peak},
+            "l2": "flushed between launches"}
+
+
+def measure_jacobian(torch, ac, dev, rank, world, K, fp32_peak_tflops, rank_max, barrier, clocks, windows):
+    """Jacobian evals/s over all N ranks (no collective on the data path; time = max over ranks)."""
+    import ctypes as C
+    from aircraft_b200 import _cabi
+    from aircraft_b200.workloads import make_controls, make_states
     peaks, peak_src = measured_peaks()
+    out = {"unit": "jacobian-evals/s", "n_gpus": world, "bytes_per_eval": B_JAC}
+    audit = kernel_audit("linearize_tile")
+
+    # ---- config 3: 65 536 x 100 nodes PER GPU, SoA outputs (7.7 GB written per launch: larger than L2)
+    n_unique, rep = 655_360, 10
+    x = torch.tensor(make_states(n_unique, seed=300 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev)
+    u = torch.tensor(make_controls(n_unique, seed=300 + rank).T, dtype=torch.float32, device=dev)
+    x, u = x.repeat(1, rep).contiguous(), u.repeat(1, rep).contiguous()
+    n = x.shape[1]
+    barrier()
+    t_mark = clocks.mark()
+    ms = rank_max(time_launches(torch, lambda: ac.linearize(x, u, DT, layout="soa"), K, 3, None))
+    windows.append((t_mark, clocks.mark()))
+    gbs = n * B_JAC / (ms * 1e-3) / 1e9
+    ex = audit["executed_fp32_flops_per_unit"] if audit else None
+    roof = {"kernel": "linearize_tile_kernel<128,soa>", "bound": "fp32 (reported in GB/s as north_star asks; intensity "
+            "~25 flop/B is above the machine balance ~11)", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+            "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src, "bytes_per_eval": B_JAC,
+            "traffic": audit["dram_bytes_per_unit"] * n if audit else None,
+            "traffic_source": (f"profiles/{audit['capture']} via profiles/r2_kernel_audit.json, {audit['dram_bytes_per_unit']:.0f} B "
+                               f"per eval scaled to this launch; CUDA sources "
+                               f"{'CHANGED since' if audit['stale'] else 'unchanged since'} the capture") if audit else None}
+    if ex:
+        roof.update({"executed_flops_per_eval": ex, "tflops_executed": n * ex / (ms * 1e-3) / 1e12,
+                     "frac_fp32_executed": n * ex / (ms * 1e-3) / 1e12 / fp32_peak_tflops,
+                     "fp32_peak": fp32_peak_tflops})
+    out["c3"] = {"workload": f"BASELINE config 3: 65 536 x 100 shooting nodes per GPU ({n * world} in total), A and B at every "
+                             "node, SoA (7.7 GB written per GPU per launch: larger than L2)",
+                 "scaling": "weak", "nodes_per_gpu": n, "ms_per_launch": ms, "value": n * world / (ms * 1e-3), "roofline": roof}
+    out["value"] = out["c3"]["value"]
+    del x, u
+
+    # ---- config 5 EXACTLY: 8192 windows x 50 nodes in total, sharded over the ranks, AoS blocks [.,13,13], [.,13,7]
+    from aircraft_b200.sharding import shard_range
+    a5, b5 = shard_range(8192, rank, world)
+    n5 = (b5 - a5) * 50
+    xw = torch.tensor(make_states(n5, seed=500 + rank, perturb_norm=1e-3), dtype=torch.float32, device=dev).view(-1, 50, 13)
+    uw = torch.tensor(make_controls(n5, seed=500 + rank), dtype=torch.float32, device=dev).view(-1, 50, 7)
+    flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+    barrier()
+    ms5 = rank_max(time_launches(torch, lambda: ac.linearize(xw, uw, DT), K, 3, flush))
+    out["c5"] = {"workload": "BASELINE config 5 exactly: 8192 windows x 50 nodes in total over the N GPUs "
+                             f"({n5} nodes on this rank), state + control Jacobians, AoS",
+                 "scaling": "strong", "nodes_total": 8192 * 50, "ms_per_launch": ms5, "value": 8192 * 50 / (ms5 * 1e-3),
+                 "gbs": 8192 * 50 * B_JAC / (ms5 * 1e-3) / 1e9, "l2": "flushed between launches"}
+
+    # ---- e2e: the same config-5 shard through the C-ABI host entry point with PINNED host buffers
+    xh = torch.empty((n5, 13), dtype=torch.float32).pin_memory(); xh.copy_(xw.view(-1, 13))
+    uh = torch.empty((n5, 7), dtype=torch.float32).pin_memory(); uh.copy_(uw.view(-1, 7))
+    xn_h = torch.empty((n5, 13), dtype=torch.float32).pin_memory()
+    A_h = torch.empty((n5, 13, 13), dtype=torch.float32).pin_memory()
+    B_h = torch.empty((n5, 13, 7), dtype=torch.float32).pin_memory()
+    lib, h = ac._lib, ac.handle
+
+    def e2e_step():
+        rc = lib.airc_linearize_host(h, xh.data_ptr(), uh.data_ptr(), DT, None, n5, 1, _cabi.FLAG_NORMALISE,
+                                     _cabi.LAYOUT_AOS, xn_h.data_ptr(), A_h.data_ptr(), B_h.data_ptr())
+        assert rc == 0
+        return float(A_h[0, 3, 3])
+
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    Ke = max(3, min(K, 10))
+    t0 = time.perf_counter()
+    for _ in range(Ke):
+        e2e_step()
+    el = rank_max(time.perf_counter() - t0)
+    out["e2e"] = {"value": 8192 * 50 * Ke / el, "unit": "jacobian-evals/s", "workload": "config 5",
+                  "h2d_bytes_per_step": n5 * 80, "d2h_bytes_per_step": n5 * 1092, "steps": Ke,
+                  "path": "airc_linearize_host (C ABI; pinned host x, u in; x+, A, B out; PCIe-bound: 1 092 B per node)"}
+    return out
+
+
+def side_extras(torch, ac, dev, args):
+    """Side lines measured on rank 0 only (device-timed, CUDA events)."""
+    from aircraft_b200.workloads import make_controls, make_states
+    out = {}
+    rank = 0
     flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)   # 256 MB > 126 MB L2
     K = max(5, min(args.steps, 20))
 
@@ -564,45 +742,6 @@ def side_measurements(torch, ac, dev, rank, args):
                                       "path": "airc_rollout_host (PCIe-bound: the control tensor crosses the bus)"}}
         del x0, U, x0_h, U_h
 
-    # config 2: 4096 rollouts x 200 from trim states (latency case)
-    if args.workload != "c2":
-        xs, us = trim_states(ac, 4096, seed=rank)
-        x0 = torch.tensor(xs.T, dtype=torch.float32, device=dev).contiguous()
-        U = device_control_sequences(torch, 4096, H_ROLL, seed=200 + rank, device=dev)
-        ms_default = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True), K, 3, flush)
-        ms = time_launches(torch, lambda: ac.rollout(x0, U, DT, layout="soa", cost=True, cooperative=True), K, 3, flush)
-        out["c2"] = {"workload": "BASELINE config 2: 4096 rollouts x horizon 200 from trim states, 1 GPU; latency mode "
-                                 "(AIRC_FLAG_COOPERATIVE: 4 lanes per trajectory); default one-trajectory kernel under ms_default",
-                     "ms_default": ms_default,
-                     "value": 4096 * H_ROLL / (ms * 1e-3), "unit": "state-steps/s", "ms_per_launch": ms,
-                     "tflops": 4096 * H_ROLL * F_STEP / (ms * 1e-3) / 1e12, "l2": "flushed between launches"}
-
-    # config 3: 65 536 x 100 nodes, (x+, A, B) at every node, SoA outputs (7.7 GB written)
-    n_unique, rep = 655_360, 10
-    x = torch.tensor(make_states(n_unique, seed=300 + rank, perturb_norm=1e-3).T, dtype=torch.float32, device=dev)
-    u = torch.tensor(make_controls(n_unique, seed=300 + rank).T, dtype=torch.float32, device=dev)
-    x, u = x.repeat(1, rep).contiguous(), u.repeat(1, rep).contiguous()
-    n = x.shape[1]
-    ms = time_launches(torch, lambda: ac.linearize(x, u, DT, layout="soa"), K, 3, None)
-    gbs = n * B_JAC / (ms * 1e-3) / 1e9
-    out["c3"] = {"workload": "BASELINE config 3: 65 536 x 100 multiple-shooting nodes, dPhi/dx and dPhi/du at every node",
-                 "value": n / (ms * 1e-3), "unit": "jacobian-evals/s", "nodes": n, "ms_per_launch": ms,
-                 "l2": "outputs (7.7 GB) larger than L2",
-                 "roofline": {"kernel": "linearize_kernel", "bound": "hbm", "achieved": gbs,
-                              "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": gbs / peaks["hbm_gbs"],
-                              "peak_source": peak_src, "bytes_per_eval": B_JAC, "traffic": None,
-                              "tflops_est": n * F_JAC / (ms * 1e-3) / 1e12}}
-    del x, u
-
-    # config 5 shard: 8192 windows x 50 nodes over 8 GPUs = 51 200 nodes per GPU (latency-bound)
-    n5 = 8192 * 50 // 8
-    x = torch.tensor(make_states(n5, seed=500 + rank, perturb_norm=1e-3), dtype=torch.float32, device=dev)
-    u = torch.tensor(make_controls(n5, seed=500 + rank), dtype=torch.float32, device=dev)
-    xw, uw = x.view(-1, 50, 13), u.view(-1, 50, 7)
-    ms = time_launches(torch, lambda: ac.linearize(xw, uw, DT), K, 3, flush)
-    out["c5_shard"] = {"workload": "BASELINE config 5 shard: 1024 windows x 50 nodes per GPU, A[.,13,13], B[.,13,7] (AoS)",
-                       "value": n5 / (ms * 1e-3), "unit": "jacobian-evals/s", "ms_per_launch": ms,
-                       "l2": "flushed between launches"}
     # config 1: ONE trajectory x 100 steps (the reference's own CPU-runnable case): latency per step
     x1 = torch.tensor(make_states(1, seed=1, level=True), dtype=torch.float32, device=dev)
     U1 = device_control_sequences(torch, 1, 100, seed=11, device=dev).permute(2, 0, 1).contiguous()   # [1,100,7]
