@@ -58,6 +58,7 @@ AIRC_HD float poly_alpha_only(const float w[NPOLY + 1], float a) {
 }
 
 struct NetAlt {
+  static constexpr bool kPolyTrig = false;   // table models keep the CUDA math library atan2f / asinf
   const AltParams* A;
 
   template <bool WITH_JAC>

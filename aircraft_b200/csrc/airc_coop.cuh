@@ -36,6 +36,7 @@ AIRC_HD F2 group_sum2(F2 v) {
 
 template <int L>
 struct NetCoop {
+  static constexpr bool kPolyTrig = true;
   const FusedNet* net;   // shared-memory copy when L > 1 (lane-dependent addresses)
   int lane;              // 0..L-1 within the node group
 

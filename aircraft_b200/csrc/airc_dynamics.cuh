@@ -173,6 +173,7 @@ AIRC_HD void surrogate(const FusedNet& net, float qbar, float alpha, float beta,
 // How the network is evaluated: by this thread alone (NetFull) or shared among the lanes that
 // cooperate on one node (NetCoop in airc_coop.cuh).
 struct NetFull {
+  static constexpr bool kPolyTrig = true;   // alpha, beta by the packed polynomial atan2 (airc_math.cuh)
   const FusedNet* net;
   template <bool WITH_JAC>
   AIRC_HD void eval(float qbar, float alpha, float beta, const Ctl& c, float C[6], float J[6][5]) const {
@@ -199,17 +200,33 @@ AIRC_HD void f_eval_net(const DevConst& P, const Net& net, const float v[3], con
     s.vbr[i] = a * s.inv_n2;
     s.vb[i] = s.vbr[i] + P.eps;
   }
-  const float vb2 = fmaf(s.vb[2], s.vb[2], fmaf(s.vb[1], s.vb[1], s.vb[0] * s.vb[0]));
+  const float xz2 = fmaf(s.vb[2], s.vb[2], s.vb[0] * s.vb[0]);
+  const float vb2 = fmaf(s.vb[1], s.vb[1], xz2);
   s.qbar = 0.6125f * vb2;                                   // 0.5*1.225*|v_b|^2   base.py:240
-  float V;
-  sqrt_rsqrt(vb2 + P.eps, V, s.invV);                       // base.py:167
   s.xa = s.vb[0] + P.eps;
-  s.alpha = atan2_acc(s.vb[2], s.xa);                       // base.py:176
-  s.sb = s.vb[1] * s.invV;
-  s.beta = asin_acc(s.sb);                                  // base.py:234
-  if (WITH_JAC) {
-    s.inv_den_a = rcp_nr(fmaf(s.xa, s.xa, s.vb[2] * s.vb[2]));
-    s.inv_cosb = fast_rsqrt(fmaf(-s.sb, s.sb, 1.0f));
+  if constexpr (Net::kPolyTrig) {
+    // NN path: alpha and beta from one packed evaluation of the branch-free polynomial atan2;
+    // asin(vb_y / V) == atan2(vb_y, sqrt(vb_x^2 + vb_z^2 + eps))            base.py:167,176,234
+    float rxz, inv_rxz;
+    sqrt_rsqrt(xz2 + P.eps, rxz, inv_rxz);                  // V cos(beta)
+    alpha_beta(s.vb[2], s.xa, s.vb[1], rxz, s.alpha, s.beta);
+    if (WITH_JAC) {
+      float V;
+      sqrt_rsqrt(vb2 + P.eps, V, s.invV);                   // base.py:167
+      s.sb = s.vb[1] * s.invV;
+      s.inv_den_a = rcp_nr(fmaf(s.xa, s.xa, s.vb[2] * s.vb[2]));
+      s.inv_cosb = inv_rxz * V;                             // 1/cos(beta) = V / sqrt(vb_x^2 + vb_z^2 + eps)
+    }
+  } else {
+    float V;
+    sqrt_rsqrt(vb2 + P.eps, V, s.invV);                     // base.py:167
+    s.alpha = atan2_acc(s.vb[2], s.xa);                     // base.py:176
+    s.sb = s.vb[1] * s.invV;
+    s.beta = asin_acc(s.sb);                                // base.py:234
+    if (WITH_JAC) {
+      s.inv_den_a = rcp_nr(fmaf(s.xa, s.xa, s.vb[2] * s.vb[2]));
+      s.inv_cosb = fast_rsqrt(fmaf(-s.sb, s.sb, 1.0f));
+    }
   }
 
   net.template eval<WITH_JAC>(s.qbar, s.alpha, s.beta, c, s.C, J);

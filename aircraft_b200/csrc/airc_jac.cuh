@@ -57,14 +57,6 @@ struct alignas(16) Q4 {
   float a, b, c, d;
 };
 
-// alpha = atan2(vb_z, vb_x + eps) and beta = asin(vb_y / V) = atan2(vb_y, sqrt(vb_x^2 + vb_z^2 + eps)) in one
-// packed evaluation of the branch-free polynomial atan2 (airc_packed.cuh).
-AIRC_HD void alpha_beta(float vbz, float xa, float vby, float rxz, float& alpha, float& beta) {
-  const F2 r = atan2_2(F2{vbz, vby}, F2{xa, rxz});
-  alpha = r.lo;
-  beta = r.hi;
-}
-
 // f(x,u) at one stage point (base.py:385-406) together with the non-zero blocks of its Jacobian, written to
 // r[0..81].  Mathematics as f_eval_net / f_tangent_t (airc_dynamics.cuh, airc_tangent.cuh), factored:
 //   D  = d v_b / d(v,q)            3x7   (closed form of d(M^T v / |q|^2))

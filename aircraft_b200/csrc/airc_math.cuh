@@ -237,8 +237,54 @@ AIRC_HD void sigm2_pair(float h0, float h1, float& r0, float& r1) {
 }
 
 // ---------------------------------------------------------------- inverse trig
-// Round-1 versions call the CUDA math library (accurate to 2 ulp); they are 8 calls per
-// RK4 step against 128 logistic evaluations.
+AIRC_HD F2 neg2(const F2& a) { return F2{-a.lo, -a.hi}; }
+AIRC_HD float sel(bool c, float a, float b) { return c ? a : b; }
+
+// atan2(y, x), all quadrants, branch-free (an infinite argument yields NaN: a diverged
+// trajectory is reported as NaN one step earlier than libm would).  atan(t) = t + t s Q(s), s = t^2, t in [0,1]:
+// degree-8 near-minimax Q (max error 6.3e-8 abs, 8.5e-8 rel incl. FP32 evaluation).
+AIRC_HD F2 atan2_2(const F2& y, const F2& x) {
+  const F2 ax{fabsf(x.lo), fabsf(x.hi)}, ay{fabsf(y.lo), fabsf(y.hi)};
+  // selects instead of min/max so that a NaN argument reaches t (FMNMX would drop it)
+  const bool glo = ay.lo > ax.lo, ghi = ay.hi > ax.hi;
+  const F2 mx{sel(glo, ay.lo, ax.lo), sel(ghi, ay.hi, ax.hi)};
+  const F2 mn{sel(glo, ax.lo, ay.lo), sel(ghi, ax.hi, ay.hi)};
+  // t = mn/mx: MUFU.RCP (1 ulp) + a residual correction of the quotient (~1 ulp); 0/0 -> t = 0
+  const F2 r{fast_rcp(mx.lo == 0.0f ? 1.0f : mx.lo), fast_rcp(mx.hi == 0.0f ? 1.0f : mx.hi)};
+  F2 t = mul2(mn, r);
+  t = fma2(fma2(neg2(t), mx, mn), r, t);      // one residual step on the quotient: no Newton step on r needed
+  const F2 s = mul2(t, t);
+  F2 q = bc2(-2.447031215e-03f);
+  q = fma2(q, s, bc2(1.375028427e-02f));
+  q = fma2(q, s, bc2(-3.627017439e-02f));
+  q = fma2(q, s, bc2(6.284360929e-02f));
+  q = fma2(q, s, bc2(-8.673170879e-02f));
+  q = fma2(q, s, bc2(1.103799429e-01f));
+  q = fma2(q, s, bc2(-1.427911092e-01f));
+  q = fma2(q, s, bc2(1.999976600e-01f));
+  q = fma2(q, s, bc2(-3.333333195e-01f));
+  F2 p = fma2(mul2(t, s), q, t);
+  // |y| > |x| : pi/2 - p ;  x < 0 : pi - p ;  sign of y
+  const float hp = 1.57079632679f, pi = 3.14159265359f;
+  p.lo = sel(glo, hp - p.lo, p.lo);
+  p.hi = sel(ghi, hp - p.hi, p.hi);
+  p.lo = sel(x.lo < 0.0f, pi - p.lo, p.lo);
+  p.hi = sel(x.hi < 0.0f, pi - p.hi, p.hi);
+  p.lo = copysignf(p.lo, y.lo);
+  p.hi = copysignf(p.hi, y.hi);
+  return p;
+}
+
+// alpha = atan2(vb_z, vb_x + eps) and beta = asin(vb_y / V) = atan2(vb_y, sqrt(vb_x^2 + vb_z^2 + eps)) in ONE packed
+// evaluation of the polynomial (base.py:167,176,234): ~35 instructions, no branches, no libm call.
+AIRC_HD void alpha_beta(float vbz, float xa, float vby, float rxz, float& alpha, float& beta) {
+  const F2 r = atan2_2(F2{vbz, vby}, F2{xa, rxz});
+  alpha = r.lo;
+  beta = r.hi;
+}
+
+// The CUDA math library versions (2 ulp) remain for the registry's table models and the jets (airc_alt.cuh,
+// airc_jet.cuh), which are not latency-critical.
 AIRC_HD float atan2_acc(float y, float x) { return atan2f(y, x); }
 AIRC_HD float asin_acc(float x) { return asinf(x); }
 

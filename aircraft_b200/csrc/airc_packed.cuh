@@ -47,7 +47,6 @@ AIRC_HD void make_unit_net(const FusedNet& f, UnitNet& n) {
 
 // ---------------------------------------------------------------- packed helpers
 AIRC_HD F2 sub2(const F2& a, const F2& b) { return fma2(bc2(-1.0f), b, a); }   // a - b, one FFMA2
-AIRC_HD F2 neg2(const F2& a) { return F2{-a.lo, -a.hi}; }
 AIRC_HD F2 fmas(float a, const F2& b, const F2& c) { return fma2(bc2(a), b, c); }     // scalar * pair + pair
 AIRC_HD F2 fmass(float a, const F2& b, float c) { return fma2(bc2(a), b, bc2(c)); }   // scalar * pair + scalar
 AIRC_HD F2 muls(float a, const F2& b) { return mul2(bc2(a), b); }
@@ -66,43 +65,6 @@ AIRC_HD void sqrt_rsqrt2(const F2& x, F2& s, F2& rs) {   // sqrt and 1/sqrt, x >
   const F2 e = fma2(neg2(xr), h, bc2(0.5f));
   s = fma2(xr, e, xr);
   rs = fma2(r, e, r);
-}
-
-AIRC_HD float sel(bool c, float a, float b) { return c ? a : b; }
-
-// atan2(y, x), all quadrants, branch-free (an infinite argument yields NaN: a diverged
-// trajectory is reported as NaN one step earlier than libm would).  atan(t) = t + t s Q(s), s = t^2, t in [0,1]:
-// degree-8 near-minimax Q (max error 6.3e-8 abs, 8.5e-8 rel incl. FP32 evaluation).
-AIRC_HD F2 atan2_2(const F2& y, const F2& x) {
-  const F2 ax{fabsf(x.lo), fabsf(x.hi)}, ay{fabsf(y.lo), fabsf(y.hi)};
-  // selects instead of min/max so that a NaN argument reaches t (FMNMX would drop it)
-  const bool glo = ay.lo > ax.lo, ghi = ay.hi > ax.hi;
-  const F2 mx{sel(glo, ay.lo, ax.lo), sel(ghi, ay.hi, ax.hi)};
-  const F2 mn{sel(glo, ax.lo, ay.lo), sel(ghi, ax.hi, ay.hi)};
-  // t = mn/mx: MUFU.RCP (1 ulp) + a residual correction of the quotient (~1 ulp); 0/0 -> t = 0
-  const F2 r{fast_rcp(mx.lo == 0.0f ? 1.0f : mx.lo), fast_rcp(mx.hi == 0.0f ? 1.0f : mx.hi)};
-  F2 t = mul2(mn, r);
-  t = fma2(fma2(neg2(t), mx, mn), r, t);      // one residual step on the quotient: no Newton step on r needed
-  const F2 s = mul2(t, t);
-  F2 q = bc2(-2.447031215e-03f);
-  q = fma2(q, s, bc2(1.375028427e-02f));
-  q = fma2(q, s, bc2(-3.627017439e-02f));
-  q = fma2(q, s, bc2(6.284360929e-02f));
-  q = fma2(q, s, bc2(-8.673170879e-02f));
-  q = fma2(q, s, bc2(1.103799429e-01f));
-  q = fma2(q, s, bc2(-1.427911092e-01f));
-  q = fma2(q, s, bc2(1.999976600e-01f));
-  q = fma2(q, s, bc2(-3.333333195e-01f));
-  F2 p = fma2(mul2(t, s), q, t);
-  // |y| > |x| : pi/2 - p ;  x < 0 : pi - p ;  sign of y
-  const float hp = 1.57079632679f, pi = 3.14159265359f;
-  p.lo = sel(glo, hp - p.lo, p.lo);
-  p.hi = sel(ghi, hp - p.hi, p.hi);
-  p.lo = sel(x.lo < 0.0f, pi - p.lo, p.lo);
-  p.hi = sel(x.hi < 0.0f, pi - p.hi, p.hi);
-  p.lo = copysignf(p.lo, y.lo);
-  p.hi = copysignf(p.hi, y.hi);
-  return p;
 }
 
 // ---------------------------------------------------------------- state, controls

@@ -121,7 +121,9 @@ def test_sharded_sweep_single_process(ac):
     assert torch.equal(res.all_cost, full.cost)
     j = int(torch.where(torch.isnan(full.cost), torch.full_like(full.cost, float("inf")), full.cost).argmin())
     assert res.argmin == j and res.owner == 0
-    assert torch.equal(res.best_trajectory, full.trajectory[j])
+    # the winner is re-rolled by a single-trajectory launch (another instantiation of the kernel: FMA contraction may
+    # differ in the last bit, which 25 free-running steps carry along)
+    assert col_err(res.best_trajectory.cpu(), full.trajectory[j].cpu(), batch_axes=(0,)) < 5e-6
     assert torch.equal(res.best_controls, f32(U[j]))
 
 
