@@ -22,7 +22,6 @@ struct AircHandle {
   DevConst dc;
   UnitNet un;          // the surrogate in unit-major order for the packed (two-trajectory) kernels
   int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0: table models (scalar kernels only)
-  int coop = 0;        // non-zero only in A/B build variants (small-batch rollouts on the lanes-per-trajectory kernel)
   int device;
   int sm_count;
   // used only by the *_host entry points (those are not re-entrant per handle)
@@ -103,9 +102,6 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   make_unit_net(h->dc.net, h->un);
 #ifdef AIRC_AB_ROLLOUT_IMPL        // build-variant A/B only (profiles/build_variants.py): 0 scalar only, 2 packed always
   h->packed = AIRC_AB_ROLLOUT_IMPL;
-#endif
-#ifdef AIRC_AB_ROLLOUT_COOP        // build-variant A/B only: 1 auto, 2/4/8 force that many lanes per trajectory
-  h->coop = AIRC_AB_ROLLOUT_COOP;
 #endif
   h->device = device;
   h->sm_count = prop.multiProcessorCount;
@@ -239,23 +235,17 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
     else rollout_kernel<false, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
     return check_launch();
   }
-  // small batches (latency case, config 2), opt-in by AIRC_FLAG_COOPERATIVE: 8 / 4 / 2 lanes per trajectory while
-  // the batch still fits one warp per sub-partition.
-  if (h->packed == 1 && (h->coop || (flags & AIRC_FLAG_COOPERATIVE)) && B * 2 <= (long long)h->sm_count * 128) {
-    const long long slots = (long long)h->sm_count * 128;          // threads of one warp per sub-partition
-    const int L = h->coop > 1 ? h->coop : (B * 8 <= slots ? 8 : (B * 4 <= slots ? 4 : 2));
-    const unsigned gridc = (unsigned)((B * L + 127) / 128);
-#define AIRC_COOP_LAUNCH(LL)                                                                             \
-    do {                                                                                                 \
-      if (cost && X) rollout_coop_kernel<true, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);              \
-      else if (cost) rollout_coop_kernel<true, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);             \
-      else if (X) rollout_coop_kernel<false, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);                \
-      else rollout_coop_kernel<false, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);                      \
-    } while (0)
-    if (L == 8) AIRC_COOP_LAUNCH(8);
-    else if (L == 4) AIRC_COOP_LAUNCH(4);
-    else AIRC_COOP_LAUNCH(2);
-#undef AIRC_COOP_LAUNCH
+  // small batches (latency case, configs 1 and 2): 8 lanes per trajectory (airc_coop.cuh).  The default while the
+  // batch leaves SM sub-partitions idle on the one-trajectory kernel (B <= 32 x SM count); AIRC_FLAG_COOPERATIVE
+  // extends it to 64 x SM count.  4 / 2 lanes and a packed-pair variant measured slower at every size
+  // (profiles/r2_variants_latency.txt).
+  if (h->packed == 1 && !(flags & AIRC_FLAG_PACKED) &&
+      (B <= (long long)h->sm_count * 32 || ((flags & AIRC_FLAG_COOPERATIVE) && B <= (long long)h->sm_count * 64))) {
+    const unsigned gridc = (unsigned)((B * 8 + 127) / 128);
+    if (cost && X) rollout_coop_kernel<true, true, 8><<<gridc, 128, 0, st>>>(h->dc, a);
+    else if (cost) rollout_coop_kernel<true, false, 8><<<gridc, 128, 0, st>>>(h->dc, a);
+    else if (X) rollout_coop_kernel<false, true, 8><<<gridc, 128, 0, st>>>(h->dc, a);
+    else rollout_coop_kernel<false, false, 8><<<gridc, 128, 0, st>>>(h->dc, a);
     return check_launch();
   }
   if (h->packed == 2 || (h->packed == 1 && ((flags & AIRC_FLAG_PACKED) || B >= 2 * wave2))) {
