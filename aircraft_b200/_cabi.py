@@ -55,6 +55,7 @@ class AircSweepParams(C.Structure):
 
 
 SWEEP_RECORD_HEADER = 4
+SWEEP_STATIC_WORKSPACE_BYTES = 32 << 20   # AIRC_SWEEP_STATIC_WORKSPACE_BYTES
 NDIAG = 22
 NZ = 21          # z = (x 13, u 7, dt): AIRC_NZ
 DIAG_SLICES = {"v_frd_rel": slice(0, 3), "airspeed": 3, "alpha": 4, "beta": 5, "qbar": 6,
@@ -96,6 +97,7 @@ PROTOTYPES = {
     "airc_sweep_workspace_bytes": (C.c_size_t, [_i64, _i32, _i32]),
     "airc_sweep": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _SP, _CP, _vp, C.c_size_t,
                              _vp, _vp, _vp]),
+    "airc_sweep_static": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _SP, _CP, _vp, _vp, _vp]),
     "airc_select_record": (C.c_int, [_vp, _vp, _i32, _i64, _vp, _vp]),
     "airc_sweep_controls": (C.c_int, [_vp, _vp, _i32, _SP, _i64, _i64, _i32, _vp, _vp]),
     "airc_sweep_host": (C.c_int, [_vp, _vp, _vp, _f, _i64, _i32, _i32, _u32, _SP, _CP, _vp, _vp]),

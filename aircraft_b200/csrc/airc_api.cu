@@ -564,6 +564,52 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
   return check_launch();
 }
 
+// ---- airc_sweep_static: the sweep on a workspace that lives in the library image (no allocation at call time).
+// In this translation unit's HOST code the name g_sweep_static_ws is only a host-side stand-in for the device
+// array: its device address comes from cudaGetSymbolAddress, once per device with that device current, and that
+// address is what the kernels receive.
+static __device__ __align__(256) unsigned char g_sweep_static_ws[AIRC_SWEEP_STATIC_WORKSPACE_BYTES];
+
+static int sweep_static_workspace(int device, void** out) {
+  enum { MAX_DEV = 64 };
+  static void* ptrs[MAX_DEV];            // per-device address, filled by the first call for that device
+  static int state[MAX_DEV];             // 0 unresolved, 1 resolved
+  if (device < 0 || device >= MAX_DEV) return fail(AIRC_EINVAL, "airc_sweep_static: device index out of range%s", "");
+  if (__atomic_load_n(&state[device], __ATOMIC_ACQUIRE) != 1) {
+    DeviceGuard g(device);
+    if (!g.ok) return fail(AIRC_ECUDA, "cudaSetDevice failed%s", "");
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_sweep_static_ws));
+    if (!p) return fail(AIRC_ECUDA, "airc_sweep_static: cudaGetSymbolAddress returned NULL%s", "");
+    ptrs[device] = p;                    // threads racing here all resolve the same address
+    __atomic_store_n(&state[device], 1, __ATOMIC_RELEASE);
+  }
+  *out = ptrs[device];
+  return AIRC_OK;
+}
+
+int airc_sweep_static(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+                      int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+                      float* cost, float* record, void* stream) {
+  if (!h || !sp || B < 0 || H < 0) return fail(AIRC_EINVAL, "airc_sweep_static: bad argument%s", "");
+  const size_t need = airc_sweep_workspace_bytes(B, H, sp->ckpt_interval);
+  if (need > (size_t)AIRC_SWEEP_STATIC_WORKSPACE_BYTES) {
+    snprintf(g_err, sizeof(g_err),
+             "airc_sweep_static: B=%lld x H=%d needs %zu bytes of workspace, the static array holds %zu "
+             "(AIRC_SWEEP_STATIC_WORKSPACE_BYTES); use airc_sweep with a caller-owned workspace",
+             (long long)B, H, need, (size_t)AIRC_SWEEP_STATIC_WORKSPACE_BYTES);
+    return AIRC_EINVAL;
+  }
+  void* ws = nullptr;
+  const int rc = sweep_static_workspace(h->device, &ws);
+  if (rc) return rc;
+  // airc_sweep's prep kernel resets the arg-min key, the thrust term and the hand-over flags on the stream at the
+  // start of every call, and every checkpoint / slice slot is written before it is read: nothing that the array
+  // still holds from the previous call is consumed.
+  return airc_sweep(h, x0, U_nom, dt, B, H, substeps, flags, sp, cp, ws, (size_t)AIRC_SWEEP_STATIC_WORKSPACE_BYTES,
+                    cost, record, stream);
+}
+
 int airc_select_record(const AircHandle* h, const float* records, int n, int64_t record_floats,
                        float* out_record, void* stream) {
   if (!h || !records || !out_record || n < 1 || record_floats < AIRC_SWEEP_RECORD_HEADER)

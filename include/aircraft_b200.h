@@ -268,6 +268,25 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
                int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
                void* workspace, size_t workspace_bytes, float* cost, float* record, void* stream);
 
+/* airc_sweep WITHOUT a caller workspace and without any allocation at call time.  No counterpart in the reference:
+ * added for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  The workspace is a file-scope `static __device__`
+ * array of AIRC_SWEEP_STATIC_WORKSPACE_BYTES inside the library image: every GPU that loads the library holds
+ * it until the process exits.  x0, U_nom, cost (optional) and record are the caller's DEVICE buffers exactly as
+ * for airc_sweep; results are those of airc_sweep with a workspace of airc_sweep_workspace_bytes(B, H, ckpt).
+ *  - limit: airc_sweep_workspace_bytes(B, H, sp->ckpt_interval) <= AIRC_SWEEP_STATIC_WORKSPACE_BYTES (32 MiB);
+ *    B = 16384 x H = 200 at the default checkpoint interval needs 26.9 MiB.  Larger sweeps return AIRC_EINVAL
+ *    with the two sizes in airc_last_error() -- use airc_sweep with your own workspace for those.
+ *  - calls no cudaMalloc / cudaFree / allocating library routine.  The first call on a device resolves the
+ *    array's device address (cudaGetSymbolAddress, once per device): make that call before a graph capture starts.
+ *  - every call on a device shares the one array; it keeps the last call's contents, and each call resets on its
+ *    stream what must start clean (arg-min key, hand-over flags).  Calls that overlap on the GPU (two streams,
+ *    two handles, two threads) RACE on it: serialise them, or give all but one a workspace through airc_sweep. */
+#define AIRC_SWEEP_STATIC_WORKSPACE_BYTES (32u << 20)
+int airc_sweep_static(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
+                      int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
+                      float* cost, float* record, void* stream);
+
 /* Picks the best of n records (lowest cost, ties to the lower global index, NaN last) laid out
  * with a stride of record_floats -- the step after an all-gather of per-rank records. */
 int airc_select_record(const AircHandle* h, const float* records, int n, int64_t record_floats,
