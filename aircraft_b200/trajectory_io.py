@@ -343,6 +343,10 @@ def write_trajectories(path, groups: Mapping[str, Mapping[str, np.ndarray]]) -> 
     w = _Writer()
     top = {}
     for gname, dsets in groups.items():
+        if gname == "":                                  # datasets stored directly under the root group
+            for dn, a in dsets.items():
+                top[dn] = (w.dataset(np.asarray(a)), 0, 0, 0)
+            continue
         ents = {dn: (w.dataset(np.asarray(a)), 0, 0, 0) for dn, a in dsets.items()}
         oh, bt, hp = w.group(ents)
         top[gname] = (oh, 1, bt, hp)
@@ -354,11 +358,16 @@ def write_trajectories(path, groups: Mapping[str, Mapping[str, np.ndarray]]) -> 
 def save_iteration(path, state, control, times=None, iteration: int = 0, append: bool = True, **extra) -> None:
     """Stores one iterate as 'iteration_<k>/{state,control,times}' (+ optional lam/mu/nu ...), column per
     node like the reference (state [13, N+1], control [7, N]); with append=True existing groups of the
-    file are kept (the reference opens its files in mode 'a', main/dynamics/dynamics.py:134-139)."""
+    file are kept, datasets stored directly under the root included (the reference opens its files in mode 'a',
+    main/dynamics/dynamics.py:134-139).  The file is re-read and rewritten as a whole (O(file size) per iterate);
+    attributes (the reference's grp.attrs['timestamp']) and gzip compression of the existing content are NOT
+    preserved.  EXPERIMENTAL: the writer's output is checked by this module's own reader and structurally against
+    two reference files (tests/test_trajectory_io.py); it has never been opened by libhdf5 / h5py (neither is in
+    the image)."""
     import os
     groups: Dict[str, Dict[str, np.ndarray]] = {}
     if append and os.path.exists(path):
-        groups = {k: v for k, v in read_trajectories(path).items() if k}
+        groups = dict(read_trajectories(path))
     g = {"state": np.asarray(state, np.float64), "control": np.asarray(control, np.float64)}
     if times is not None:
         g["times"] = np.asarray(times, np.float64)

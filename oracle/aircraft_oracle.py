@@ -84,7 +84,11 @@ def _pure(v: torch.Tensor) -> torch.Tensor:
 class SurrogateF64:
     """ScaledModel.forward in float64 from the FP32 checkpoint (models.py:143-155;
     loader utils.py:30-40).  Layers: Linear(5,16) -> Linear(16,32) -> Tanh -> Linear(32,6),
-    no activation between the first two (models.py:114-123)."""
+    no activation between the first two (models.py:114-123).
+
+    dtype=torch.float32 is the L4CasADi reading of the reference (coefficient_models.py:93-100: the traced torch module
+    runs in the checkpoint's own precision inside the float64 CasADi graph): inputs are rounded to float32, the
+    network runs in float32 and its output is widened back.  Parity tests quote the GPU's error against both."""
 
     def __init__(self, path: Path | str = DEFAULT_WEIGHTS, dtype=F64):
         ck = torch.load(str(path), map_location="cpu", weights_only=True)
@@ -103,7 +107,7 @@ class SurrogateF64:
         h = h @ self.W2.T + self.b2
         h = torch.tanh(h)
         y = h @ self.W3.T + self.b3
-        return y * self.out_std + self.out_mean
+        return (y * self.out_std + self.out_mean).to(inp.dtype)
 
 
 # --------------------------------------------------------------------------- constants

@@ -65,7 +65,18 @@ def test_state_update_65536(ac, orc, substeps, normalise, dt):
     x, u = make_states(65536, seed=32), make_controls(65536, seed=32)
     want = orc.state_update(t64(x), t64(u), dt, substeps, normalise).numpy()
     got = ac.state_update(f32(x.T), f32(u.T), dt, substeps=substeps, normalise=normalise).T.cpu().numpy()
-    assert col_err(got, want) < PARITY_TOL
+    e64 = col_err(got, want)
+    # second reference: the same float64 dynamics around the network evaluated in FLOAT32, which is what L4CasADi
+    # does with the checkpoint (coefficient_models.py:93-100).  The two readings differ by ~1e-7 of a column's scale
+    # per step; the GPU is held to the bar against both.
+    from oracle.aircraft_oracle import SurrogateF64
+    orc32 = oracle_for(TRIM_COM)
+    orc32.nn = SurrogateF64(orc32.cfg.weights, dtype=torch.float32)
+    want32 = orc32.state_update(t64(x), t64(u), dt, substeps, normalise).numpy()
+    e32, e_between = col_err(got, want32), col_err(want32, want)
+    print(f"state_update 65536 substeps={substeps} normalise={normalise}: GPU vs f64-network oracle {e64:.2e}, "
+          f"GPU vs f32-network oracle {e32:.2e}, between the two oracles {e_between:.2e}")
+    assert e64 < PARITY_TOL and e32 < PARITY_TOL
 
 
 def test_state_update_per_node_dt_and_single_column(ac, orc):

@@ -92,6 +92,32 @@ def test_sweep_costs_match_explicit_kernel_and_cpu_reference(ac, ref, x0):
     assert col_err(r.trajectory.cpu().numpy(), one.cpu().numpy()) < 2e-5
 
 
+def test_full_batch_geometry_costs_match_cpu_reference(ac, ref, x0):
+    """The launch geometry of BASELINE config 4's shard (125 000 trajectories: 1 954 groups of 64 on more than one
+    wave, time-sliced into segments with slice hand-over, checkpoints on) at a horizon short enough that FP32 and
+    float64 have not yet drifted apart: ALL 125 000 costs against the float64 CPU sweep at the parity bar, and the
+    fused arg-min against it."""
+    B, H = 125000, 16
+    Un = nominal(H)
+    sp, cp = make_sweep_params(seed=21), make_cost_params()
+    r = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
+    cost = r.cost.cpu().numpy().astype(np.float64)
+    bc, bi, c64 = ref.sweep(x0, Un, DT, B, sp, cp, normalise=True)
+    assert np.isfinite(c64).all()
+    err = np.abs(cost - c64).max() / np.abs(c64).max()
+    print(f"125000 x {H} sweep: max |cost - cost_f64| / max |cost_f64| = {err:.2e}")
+    assert err <= 1e-5
+    am = int(r.argmin.item())
+    assert am == int(np.argmin(cost)) and float(r.min_cost.item()) == np.float32(cost.min())
+    order = np.sort(c64)
+    if order[1] - order[0] > 2e-5 * abs(order[0]):
+        assert am == bi
+    Uw = ref.sweep_controls(sp, Un, am, 1)[0]
+    assert np.array_equal(r.controls.cpu().numpy(), Uw)
+    Xw = ref.rollout(x0[None], Uw[None].astype(np.float64), DT, normalise=True)[0]
+    assert col_err(r.trajectory.cpu().numpy(), Xw) < 2e-5
+
+
 @pytest.mark.parametrize("ckpt", [1, 7, 8, 40, 1000])
 def test_checkpoint_interval_does_not_change_the_record(ac, x0, ckpt):
     B, H = 3000, 40
