@@ -15,12 +15,14 @@
 #include "airc_peak.cuh"
 #include "airc_sweep.cuh"
 #include "airc_sweep2.cuh"
+#include "airc_sweep2tc.cuh"
 
 using namespace airc;
 
 struct AircHandle {
   DevConst dc;
   UnitNet un;          // the surrogate in unit-major order for the packed (two-trajectory) kernels
+  TcNetImage tcn;      // the surrogate as split-TF32 operand matrices for the tensor-core sweep (airc_tc.cuh)
   int packed = 1;      // 1: sweep on the packed kernels, rollout picks by batch size; 0: table models (scalar kernels only)
   int device;
   int sm_count;
@@ -100,6 +102,7 @@ int airc_create(const AircParams* params, const AircNNBlob* nn, int device, Airc
   if (!h) return fail(AIRC_ENOMEM, "airc_create: out of host memory%s", "");
   build_devconst(*params, *nn, h->dc);
   make_unit_net(h->dc.net, h->un);
+  make_tc_net(h->un, h->tcn);
 #ifdef AIRC_AB_ROLLOUT_IMPL        // build-variant A/B only (profiles/build_variants.py): 0 scalar only, 2 packed always
   h->packed = AIRC_AB_ROLLOUT_IMPL;
 #endif
@@ -523,8 +526,28 @@ int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float d
     a.flag = flag;
     a.cc = cc; a.smp = smp; a.dt = dt; a.B = B; a.H = H; a.C = L.C; a.substeps = substeps;
     a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
+    // Large sweeps (more 128-thread tasks per segment than the machine holds at once): the surrogate's layers run
+    // on the tensor cores, one 384-thread block = three 128-thread groups per SM (airc_sweep2tc.cuh).
+#ifndef AIRC_AB_SWEEP_TC           // build-variant A/B only: 0 keeps every sweep on the FFMA2 kernel
+#define AIRC_AB_SWEEP_TC 1
+#endif
+    const bool use_tc = AIRC_AB_SWEEP_TC && full && a.gs == 64 && bs == AIRC_S2_BS && B >= (long long)h->sm_count * 3 * 256;
+    if (use_tc) {
+      const long long slots_tc = (long long)h->sm_count * 3;
+      a.GB = (a.G + 3) / 4;
+      a.S = choose_segments(a.GB, slots_tc, H);
+#ifdef AIRC_AB_SWEEP_SEGMENTS
+      a.S = AIRC_AB_SWEEP_SEGMENTS;
+#endif
+      a.L = a.S > 1 ? (H + a.S - 1) / a.S : (H > 0 ? H : 1);
+      a.S = H > 0 ? (H + a.L - 1) / a.L : 1;
+    }
     sweep2_prep_kernel<<<1, 256, 0, st>>>(U_nom, H, cc.neg_log2e_over_eps, key, thrust_du, flag, full ? a.G : 0);
-    if (B > 0) {
+    if (B > 0 && use_tc) {
+      const unsigned grid = (unsigned)(((long long)a.GB * a.S + 2) / 3);
+      if (ck) sweep2tc_kernel<true><<<grid, AIRC_S2TC_BS, 0, st>>>(h->dc, h->tcn, a);
+      else sweep2tc_kernel<false><<<grid, AIRC_S2TC_BS, 0, st>>>(h->dc, h->tcn, a);
+    } else if (B > 0) {
       const unsigned grid = (unsigned)((long long)a.GB * a.S);
       if (ck) sweep2_kernel<true><<<grid, bs, 0, st>>>(h->dc, h->un, a);
       else sweep2_kernel<false><<<grid, bs, 0, st>>>(h->dc, h->un, a);

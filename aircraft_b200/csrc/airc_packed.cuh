@@ -139,8 +139,24 @@ AIRC_HD void surrogate2(const UnitNet& net, const F2& qbar, const F2& alpha, con
   }
 }
 
+// How f gets its coefficients: on the FMA pipe from the unit-major weights (here), or on the tensor cores
+// (SurTc, airc_tc.cuh).  Everything around the surrogate is the same code for both.
+// begin() gets the network's inputs, end() delivers the coefficients; f puts the work that needs neither in between.
+struct SurFfma {
+  const UnitNet& net;
+  F2 Cs[6];
+  AIRC_HD void begin(const F2& qbar, const F2& alpha, const F2& beta, const Ctl2& c) {
+    surrogate2(net, qbar, alpha, beta, c, Cs);
+  }
+  AIRC_HD void end(F2 C[6]) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) C[k] = Cs[k];
+  }
+};
+
 // f(x,u) for two trajectories (p_dot = v is handled by the caller).  base.py:385-406.
-AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const F2 q[4],
+template <class Sur>
+AIRC_HD void f_eval2(const DevConst& P, Sur& sur, const F2 v[3], const F2 q[4],
                      const F2 w[3], const Ctl2& c, F2 vdot[3], F2 qdot[4], F2 wdot[3], F2& vb2_out) {
   F2 M[9], n2;
   rot_matrix2(q, M, n2);
@@ -164,8 +180,24 @@ AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const
   sqrt_rsqrt2(adds(xz2, P.eps), rxz, rs_unused);              // sqrt(V^2 - vb_y^2), V^2 = vb2+eps
   const F2 beta = atan2_2(vb[1], rxz);                        // == asin(vb_y/V), base.py:167,234
 
+  sur.begin(qbar, alpha, beta, c);
+  // ---- the part of f that does not need the coefficients
+  // q_dot = 0.5 q (x) (w,0)                                  base.py:292-295
+  const F2 hw0 = muls(0.5f, w[0]), hw1 = muls(0.5f, w[1]), hw2 = muls(0.5f, w[2]);
+  qdot[0] = fma2(q[3], hw0, fma2(q[1], hw2, mul2(neg2(q[2]), hw1)));
+  qdot[1] = fma2(q[3], hw1, fma2(q[2], hw0, mul2(neg2(q[0]), hw2)));
+  qdot[2] = fma2(q[3], hw2, fma2(q[0], hw1, mul2(neg2(q[1]), hw0)));
+  qdot[3] = neg2(fma2(q[0], hw0, fma2(q[1], hw1, mul2(q[2], hw2))));
+  // w x (I w)                                                base.py:376-377
+  F2 Iw[3], gy[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i)
+    Iw[i] = fmas(P.I[3 * i + 2], w[2], fmas(P.I[3 * i + 1], w[1], muls(P.I[3 * i], w[0])));
+  gy[0] = fma2(w[1], Iw[2], mul2(neg2(w[2]), Iw[1]));
+  gy[1] = fma2(w[2], Iw[0], mul2(neg2(w[0]), Iw[2]));
+  gy[2] = fma2(w[0], Iw[1], mul2(neg2(w[1]), Iw[0]));
   F2 C[6];
-  surrogate2(net, qbar, alpha, beta, c, C);
+  sur.end(C);
   C[5] = fmas(P.k_rudder, c.dr, C[5]);                        // coefficient_models.py:102-103
   if (P.stall_scaling) {                                      // aircraft.py:280-294 (default off)
     const float k = 10.0f, a30 = 0.52359877559f;
@@ -199,21 +231,11 @@ AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const
     a = fma2(M[3 * i + 2], F[2], a);
     vdot[i] = fma2(a, sc, bc2(P.g[i]));
   }
-  // q_dot = 0.5 q (x) (w,0)                                  base.py:292-295
-  const F2 hw0 = muls(0.5f, w[0]), hw1 = muls(0.5f, w[1]), hw2 = muls(0.5f, w[2]);
-  qdot[0] = fma2(q[3], hw0, fma2(q[1], hw2, mul2(neg2(q[2]), hw1)));
-  qdot[1] = fma2(q[3], hw1, fma2(q[2], hw0, mul2(neg2(q[0]), hw2)));
-  qdot[2] = fma2(q[3], hw2, fma2(q[0], hw1, mul2(neg2(q[1]), hw0)));
-  qdot[3] = neg2(fma2(q[0], hw0, fma2(q[1], hw1, mul2(q[2], hw2))));
   // w_dot = I^-1 (M - w x (I w))                             base.py:376-377
-  F2 Iw[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i)
-    Iw[i] = fmas(P.I[3 * i + 2], w[2], fmas(P.I[3 * i + 1], w[1], muls(P.I[3 * i], w[0])));
   F2 t[3];
-  t[0] = sub2(Mo[0], fma2(w[1], Iw[2], mul2(neg2(w[2]), Iw[1])));
-  t[1] = sub2(Mo[1], fma2(w[2], Iw[0], mul2(neg2(w[0]), Iw[2])));
-  t[2] = sub2(Mo[2], fma2(w[0], Iw[1], mul2(neg2(w[1]), Iw[0])));
+  t[0] = sub2(Mo[0], gy[0]);
+  t[1] = sub2(Mo[1], gy[1]);
+  t[2] = sub2(Mo[2], gy[2]);
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     wdot[i] = fmas(P.Iinv[3 * i + 2], t[2], fmas(P.Iinv[3 * i + 1], t[1], muls(P.Iinv[3 * i], t[0])));
@@ -223,7 +245,8 @@ AIRC_HD void f_eval2(const DevConst& P, const UnitNet& net, const F2 v[3], const
 // state_step for two trajectories, base.py:408-446 (all 13 components additively).
 // speed2 receives |v_b(x)|^2 of the step's FIRST stage, i.e. of the node itself: the loss's speed term
 // (control.py:63-64, aircraft.v_frd_rel on every node) costs nothing extra.
-AIRC_HD void rk4_step2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float h, F2& speed2) {
+template <class Sur>
+AIRC_HD void rk4_step2(const DevConst& P, Sur& sur, State2& x, const Ctl2& c, float h, F2& speed2) {
   const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
   F2 sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
 #pragma unroll
@@ -235,7 +258,7 @@ AIRC_HD void rk4_step2(const DevConst& P, const UnitNet& net, State2& x, const C
     const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
     const float cn = (stage == 2) ? h : hh;
     F2 kv[3], kq[4], kw[3], vb2;
-    f_eval2(P, net, sv, sq, sw, c, kv, kq, kw, vb2);
+    f_eval2(P, sur, sv, sq, sw, c, kv, kq, kw, vb2);
     if (stage == 0) speed2 = vb2;
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
@@ -271,13 +294,19 @@ AIRC_HD void normalise_q2(State2& x) {          // base.py:443-444, 473-474
 
 // Phi(x,u,dt), base.py:450-480
 // speed2: |v_b|^2 at the node x (before the update), a by-product of the first RK4 stage
-AIRC_HD void state_update2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float dt,
-                           int substeps, bool normalise, F2& speed2) {
+template <class Sur>
+AIRC_HD void state_update2_with(const DevConst& P, Sur& sur, State2& x, const Ctl2& c, float dt,
+                                int substeps, bool normalise, F2& speed2) {
   const float h = (substeps == 1) ? dt : dt / (float)substeps;
   F2 sp2;
-  rk4_step2(P, net, x, c, h, speed2);
-  for (int s = 1; s < substeps; ++s) rk4_step2(P, net, x, c, h, sp2);
+  rk4_step2(P, sur, x, c, h, speed2);
+  for (int s = 1; s < substeps; ++s) rk4_step2(P, sur, x, c, h, sp2);
   if (normalise) normalise_q2(x);
+}
+AIRC_HD void state_update2(const DevConst& P, const UnitNet& net, State2& x, const Ctl2& c, float dt,
+                           int substeps, bool normalise, F2& speed2) {
+  SurFfma sur{net};
+  state_update2_with(P, sur, x, c, dt, substeps, normalise, speed2);
 }
 
 // |v_b|^2 of the node for the speed term of the loss (control.py:63-64)

@@ -554,10 +554,12 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
                         "pinned host -> device, airc_sweep, NCCL all-gather of records, airc_select_record, record -> host"},
         "gpu_launches": launches,
         "best": {"min_cost": float(out.min_cost), "argmin": int(out.argmin)},
-        "roofline": rollout_roofline("sweep2_kernel<ckpt> (+ sweep2_prep, sweep_winner2: < 2 % of the call)",
+        "roofline": rollout_roofline("sweep2tc_kernel<ckpt>: network layers on tcgen05 (TF32 split in three, 18 432 tensor flop per "
+                                     "state-step = 0.18 of the TF32 peak), the rest on FFMA2 (+ sweep2_prep, sweep_winner2: "
+                                     "< 2 % of the call)",
                                      roll_tflops, peak, per_gpu * H, ms_roll, ms_step,
                                      "kernel_ms = CUDA events around the airc_sweep call (three launches)",
-                                     audit=kernel_audit("sweep2")),
+                                     audit=kernel_audit("sweep2tc")),
     }
 
 

@@ -263,7 +263,10 @@ int64_t airc_sweep_record_floats(int H);
 /* bytes of device workspace airc_sweep needs (checkpoints dominate: 17 floats x B per checkpoint) */
 size_t airc_sweep_workspace_bytes(int64_t B, int H, int ckpt_interval);
 
-/* x0 [13], U_nom [H][7], workspace, cost (optional, [B]) and record are DEVICE pointers. */
+/* x0 [13], U_nom [H][7], workspace, cost (optional, [B]) and record are DEVICE pointers.
+ * Sweeps of B >= 3 x 256 x SM count trajectories ('nn' model, full workspace) evaluate the network layers on the
+ * tensor cores (TF32 operands split in three, FP32 accumulation: same results to ~1e-6 relative); the record's
+ * trajectory is then re-rolled from the sweep's checkpoints with the FP32 FMA arithmetic of airc_rollout. */
 int airc_sweep(const AircHandle* h, const float* x0, const float* U_nom, float dt, int64_t B, int H,
                int substeps, uint32_t flags, const AircSweepParams* sp, const AircCostParams* cp,
                void* workspace, size_t workspace_bytes, float* cost, float* record, void* stream);
