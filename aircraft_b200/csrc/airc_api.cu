@@ -320,8 +320,12 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
       else if (want_dt) AIRC_JAC_LAUNCH(NT_, false, true);                                                  \
       else AIRC_JAC_LAUNCH(NT_, false, false);                                                              \
     } while (0)
+#if defined(AIRC_JAC_FORCE_NT) && AIRC_JAC_FORCE_NT == 32
+    AIRC_JAC_PICK(32);
+#else
     if (big) AIRC_JAC_PICK(128);
     else AIRC_JAC_PICK(64);
+#endif
 #undef AIRC_JAC_PICK
 #undef AIRC_JAC_LAUNCH
     return check_launch();

@@ -65,7 +65,7 @@ AIRC_D void jk_out_lin(float* __restrict__ g, const float* __restrict__ im, int 
 }
 
 template <int NT, bool SOA, bool DT>
-__global__ void __launch_bounds__(2 * NT, (NT == 128) ? 1 : 2)
+__global__ void __launch_bounds__(2 * NT, (NT == 128) ? 1 : ((NT == 64) ? 2 : 4))
 linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const int vec_ok) {
   using T = JacTile<NT, SOA, DT>;
   using L = JRec<DT>;

@@ -181,6 +181,81 @@ def sweep_sampled(aircraft, x0, U_nom, dt: float, total: int, *, sampler=None, c
     return out
 
 
+class SweepPlan:
+    """The whole sharded sweep step -- prep + time-sliced sweep + winner re-roll (airc_sweep), the all-gather of the
+    per-rank winner records and the device-side selection -- captured ONCE in a CUDA graph and replayed per step:
+    one graph launch instead of five host-issued operations, so the step is not bound by Python / launch latency
+    (at 8 GPUs the eager exchange adds ~35 us to a 2.3 ms sweep).  Buffers are owned by the plan; new inputs are
+    copied into `x0` / `U_nom` (device tensors) before `replay()`.  GPU + NCCL only: the gloo path of
+    sweep_sampled() stays eager.
+
+        plan = SweepPlan(aircraft, H, dt, total, sampler=..., cost=...)
+        plan.x0.copy_(x0); plan.U_nom.copy_(U_nom)
+        rec = plan.replay()            # SweepRecord of the global winner (views of plan-owned memory)
+    """
+
+    def __init__(self, aircraft, H: int, dt: float, total: int, *, sampler=None, cost=True,
+                 substeps: Optional[int] = None, normalise: Optional[bool] = None, group=None,
+                 return_costs: bool = False):
+        import ctypes as C
+        from . import _cabi
+        from .aircraft import _check
+        from .params import make_cost_params, make_sweep_params
+        ac = aircraft
+        self.aircraft, self.group, self.H = ac, group, int(H)
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        start, stop = shard_range(total, self.rank, self.world)
+        self.local = stop - start
+        sp = _cabi.AircSweepParams.from_buffer_copy(sampler) if isinstance(sampler, _cabi.AircSweepParams) \
+            else make_sweep_params(**(sampler or {}))
+        sp.index_offset = int(sp.index_offset) + start
+        cp = cost if isinstance(cost, _cabi.AircCostParams) else make_cost_params(**(cost if isinstance(cost, dict) else {}))
+        self._sp, self._cp = sp, cp
+        lib, dev = ac._lib, torch.device("cuda", int(ac._device))
+        R = int(lib.airc_sweep_record_floats(self.H))
+        wsb = int(lib.airc_sweep_workspace_bytes(self.local, self.H, sp.ckpt_interval))
+        self.x0 = torch.zeros(13, dtype=torch.float32, device=dev)
+        self.U_nom = torch.zeros((self.H, 7), dtype=torch.float32, device=dev)
+        self._ws = torch.empty(wsb, dtype=torch.uint8, device=dev)
+        self._rec = torch.empty(R, dtype=torch.float32, device=dev)
+        self._all = torch.empty((self.world, R), dtype=torch.float32, device=dev)
+        self._best = torch.empty(R, dtype=torch.float32, device=dev)
+        self.cost = torch.empty(self.local, dtype=torch.float32, device=dev) if return_costs else None
+        ns, fl = ac._substeps(substeps), ac._flags(normalise)
+
+        def enqueue():
+            st = torch.cuda.current_stream(dev).cuda_stream
+            _check(lib.airc_sweep(ac.handle, self.x0.data_ptr(), self.U_nom.data_ptr(), float(dt), self.local, self.H, ns, fl,
+                                  C.byref(sp), C.byref(cp), self._ws.data_ptr(), self._ws.numel(),
+                                  self.cost.data_ptr() if self.cost is not None else None, self._rec.data_ptr(), st),
+                   lib, "airc_sweep")
+            if self.world > 1:
+                dist.all_gather_into_tensor(self._all, self._rec.reshape(1, -1), group=group)
+                _check(lib.airc_select_record(ac.handle, self._all.data_ptr(), self.world, R, self._best.data_ptr(), st),
+                       lib, "airc_select_record")
+
+        # warm-up on a side stream (creates the NCCL communicator, loads the kernels), then capture
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(2):
+                enqueue()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            enqueue()
+        self.launches_per_replay = 1
+
+    def replay(self):
+        from .aircraft import decode_record
+        self.graph.replay()
+        out = decode_record(self._best if self.world > 1 else self._rec, self.H, self.cost)
+        out.workspace = self._ws
+        return out
+
+
 def gather_varlen(local: torch.Tensor, total: int, rank: int, world: int, group=None) -> torch.Tensor:
     """all_gather of contiguous shards whose lengths follow shard_range (differ by at most one)."""
     if world == 1:

@@ -286,3 +286,21 @@ def test_nan_in_the_nominal_sequence_propagates(ac, x0):
     assert torch.isnan(r.cost).all()
     U = ac.sweep_controls(f32(Un), make_sweep_params(seed=4), 0, 8)
     assert torch.isnan(U[:, 5, 1]).all() and torch.isfinite(U[:, :5]).all()
+
+
+def test_sweep_plan_graph_replay_equals_eager_sweep(ac, x0):
+    """SweepPlan (aircraft_b200/sharding.py): the sweep captured in a CUDA graph and replayed -- same record and
+    costs as the eager call, for new inputs copied into the plan's buffers between replays."""
+    from aircraft_b200.sharding import SweepPlan
+    B, H = 5000, 24
+    sp, cp = make_sweep_params(seed=31), make_cost_params()
+    plan = SweepPlan(ac, H, DT, B, sampler=sp, cost=cp, return_costs=True)
+    for seed in (9, 10):
+        Un = nominal(H, seed=seed)
+        plan.x0.copy_(f32(x0))
+        plan.U_nom.copy_(f32(Un))
+        got = plan.replay()
+        torch.cuda.synchronize()
+        want = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
+        assert torch.equal(got.raw, want.raw) and torch.equal(got.cost, want.cost)
+        assert int(got.argmin) == int(want.argmin)
