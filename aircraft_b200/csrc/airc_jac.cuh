@@ -9,12 +9,15 @@
 // blocks IPOPT takes from the defect constraints (control/base.py:275-286).
 //
 // Two phases per tile of NT nodes, one thread block per tile:
-//   phase 1  ONE NODE PER THREAD (no replication, no shuffles, no divergence): the primal RK4 step with the
-//            surrogate and its 6x5 Jacobian, and for each of the four stage points the non-zero blocks of
+//   phase 1  ONE NODE PER THREAD PAIR, no replication and no shuffles: the primal RK4 step with the surrogate and
+//            its 6x5 Jacobian, and for each of the four stage points the non-zero blocks of
 //            f_x (10x10 over v, q, omega: f does not read p) and f_u (aileron, elevator, rudder, flaps;
 //            thrust is inert, aircraft.py:320), assembled ONCE per node from the chain
 //            (v,q) -> v_b -> (qbar, alpha, beta) -> C -> (F, M) -> (v_dot, omega_dot)   and parked in
 //            shared memory: 84 floats per stage, 348 per node (92 / 380 with the d/d(dt) column).
+//            The two threads of a pair (in two warps on the same scheduler) alternate the stages: f_jac_head
+//            gives the primal k after a quarter of a stage's work, the next stage point goes to the partner,
+//            and f_jac_tail (the blocks) overlaps the partner's head (airc_jac_kernel.cuh).
 //   phase 2  EIGHT LANES PER NODE, one packed column pair (FFMA2) per lane: the tangent recursion above as
 //            small matrix-vector products with the parked blocks as broadcast operands (~80 FFMA2 per stage
 //            instead of ~230 for pushing a tangent through the whole of f); results go to a shared-memory
@@ -64,8 +67,71 @@ struct alignas(16) Q4 {
 //   Z  = d(F, m)/d(qbar, alpha, beta) through the surrogate Jacobian J               6x3
 //   W  = [ M/(m |q|^2) ; I^-1 [com]x , I^-1 ] Z                                      6x3
 //   [P; R](v,q) = W Y  + direct terms (d(M F)/dq at fixed F; gyroscopic d(w x Iw)/dw)
-AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const float w[3], const Ctl& c,
-                   float kv[3], float kq[4], float kw[3], float* r) {
+//
+// f_jac is cut in two so that the PRIMAL derivative k = f(X) is known after the first quarter of the work
+// (f_jac_head: geometry, the surrogate's forward pass, forces, k) and the next RK4 stage point can be handed to
+// another warp while this one assembles the Jacobian blocks (f_jac_tail: D, Y, the surrogate's derivative pass from
+// the parked logistic values, Z, W, the blocks).  Same operations in the same order as the fused form.
+struct JacMid {
+  float M[9], inv, vbr[3], vb[3], xa, invV, inv_rxz, ida, sb, qbar, alpha, beta;
+  float C[6], Craw2, Craw4, qS, sgn, F[3], lq[3], sc, acc[3], Iw[3];
+  F2 rr[NH / 2];                 // logistic values r_j of the 32 hidden units, two per entry
+};
+
+// the surrogate's forward pass (as surrogate<>, airc_dynamics.cuh), keeping r for the derivative pass
+AIRC_HD void surrogate_fwd(const FusedNet& net, float qbar, float alpha, float beta, const Ctl& c, float C[6],
+                           F2 rr[NH / 2]) {
+  F2 acc[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) acc[k] = F2{net.c0[k], 0.0f};
+  const F2 da = bc2(c.da), de = bc2(c.de), qb = bc2(qbar), al = bc2(alpha), be = bc2(beta);
+#pragma unroll
+  for (int p = 0; p < NH / 2; ++p) {
+    const HidPair& w = net.hid[p];
+    F2 h = F2{w.a0[0], w.a0[1]};
+    h = fma2b(F2{w.Au[0][0], w.Au[0][1]}, da, h);
+    h = fma2b(F2{w.Au[1][0], w.Au[1][1]}, de, h);
+    h = fma2b(F2{w.Ax[0][0], w.Ax[0][1]}, qb, h);
+    h = fma2b(F2{w.Ax[1][0], w.Ax[1][1]}, al, h);
+    h = fma2b(F2{w.Ax[2][0], w.Ax[2][1]}, be, h);
+    const F2 r = sigm2_x2(h);
+    rr[p] = r;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) acc[k] = fma2b(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, r, acc[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k) C[k] = acc[k].lo + acc[k].hi;
+}
+
+// J = Wo diag(g) W1,  g_j = d r_j / d h_j = -ln2 r (1 - r)
+AIRC_HD void surrogate_jac(const FusedNet& net, const F2 rr[NH / 2], float J[6][5]) {
+  F2 Jacc[6][5];
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+#pragma unroll
+    for (int i = 0; i < 5; ++i) Jacc[k][i] = F2{0.0f, 0.0f};
+#pragma unroll
+  for (int p = 0; p < NH / 2; ++p) {
+    const HidPair& w = net.hid[p];
+    const F2 r = rr[p];
+    const F2 g = mul2b(mul2b(r, bc2(-0.69314718056f)), F2{1.0f - r.lo, 1.0f - r.hi});
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const F2 wi = (i < 3) ? F2{w.Ax[i][0], w.Ax[i][1]} : F2{w.Au[i - 3][0], w.Au[i - 3][1]};
+      const F2 gw = mul2b(g, wi);
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        Jacc[k][i] = fma2b(F2{net.Wo[k][2 * p], net.Wo[k][2 * p + 1]}, gw, Jacc[k][i]);
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+#pragma unroll
+    for (int i = 0; i < 5; ++i) J[k][i] = Jacc[k][i].lo + Jacc[k][i].hi;
+}
+
+AIRC_HD void f_jac_head(const DevConst& P, const float v[3], const float q[4], const float w[3], const Ctl& c,
+                        float kv[3], float kq[4], float kw[3], JacMid& m) {
   // ---- v_b = M^T v / |q|^2 + eps                                      base.py:156-159
   float M[9], n2;
   rot_matrix(q, M, n2);
@@ -91,6 +157,81 @@ AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const 
   const float ida = rcp_nr(fmaf(xa, xa, vb[2] * vb[2]));
   const float sb = vb[1] * invV;
 
+
+  // ---- surrogate, forward pass                                       models.py:143-155, coefficient_models.py:99-104
+  float C[6];
+  surrogate_fwd(P.net, qbar, alpha, beta, c, C, m.rr);
+  C[5] = fmaf(P.k_rudder, c.dr, C[5]);
+  m.Craw2 = C[2];
+  m.Craw4 = C[4];
+  if (P.stall_scaling) {                                              // aircraft.py:280-294
+    const float k = 10.0f, a30 = 0.52359877559f;
+    const float sa = 1.0f / (1.0f + expf(k * (fabsf(alpha) - a30)));
+    const float sbs = 1.0f / (1.0f + expf(k * (fabsf(beta) - a30)));
+    C[2] *= sa * sbs;
+    C[4] *= sa;
+  }
+  C[0] = fmaf(P.k_flap_x, c.df, C[0]);                                // aircraft.py:297-299
+  C[2] = fmaf(P.k_flap_z, c.df, C[2]);
+
+  // ---- forces, moments, f                                            aircraft.py:313-328 ; base.py:255-297,344-383
+  const float qS = qbar * P.S;
+  const float sgn = sign_casadi(vb[0]);
+  const float F[3] = {C[0] * qS * sgn, C[1] * qS, C[2] * qS};
+  const float lq[3] = {qbar * P.Sb, qbar * P.Sc, qbar * P.Sb};
+  float Mo[3];
+  Mo[0] = C[3] * lq[0] + (P.com[1] * F[2] - P.com[2] * F[1]);
+  Mo[1] = C[4] * lq[1] + (P.com[2] * F[0] - P.com[0] * F[2]);
+  Mo[2] = C[5] * lq[2] + (P.com[0] * F[1] - P.com[1] * F[0]);
+  const float sc = inv * P.inv_mass;
+  float acc[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    float a = M[3 * i] * F[0];
+    a = fmaf(M[3 * i + 1], F[1], a);
+    a = fmaf(M[3 * i + 2], F[2], a);
+    acc[i] = a * sc;
+    kv[i] = acc[i] + P.g[i];
+  }
+  kq[0] = 0.5f * (q[3] * w[0] + (q[1] * w[2] - q[2] * w[1]));
+  kq[1] = 0.5f * (q[3] * w[1] + (q[2] * w[0] - q[0] * w[2]));
+  kq[2] = 0.5f * (q[3] * w[2] + (q[0] * w[1] - q[1] * w[0]));
+  kq[3] = -0.5f * (q[0] * w[0] + q[1] * w[1] + q[2] * w[2]);
+  float Iw[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) Iw[i] = fmaf(P.I[3 * i + 2], w[2], fmaf(P.I[3 * i + 1], w[1], P.I[3 * i] * w[0]));
+  {
+    const float t[3] = {Mo[0] - (w[1] * Iw[2] - w[2] * Iw[1]), Mo[1] - (w[2] * Iw[0] - w[0] * Iw[2]),
+                        Mo[2] - (w[0] * Iw[1] - w[1] * Iw[0])};
+#pragma unroll
+    for (int i = 0; i < 3; ++i) kw[i] = fmaf(P.Iinv[3 * i + 2], t[2], fmaf(P.Iinv[3 * i + 1], t[1], P.Iinv[3 * i] * t[0]));
+  }
+
+
+#pragma unroll
+  for (int i = 0; i < 9; ++i) m.M[i] = M[i];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    m.vbr[i] = vbr[i]; m.vb[i] = vb[i]; m.F[i] = F[i]; m.lq[i] = lq[i]; m.acc[i] = acc[i]; m.Iw[i] = Iw[i];
+  }
+#pragma unroll
+  for (int i = 0; i < 6; ++i) m.C[i] = C[i];
+  m.inv = inv; m.xa = xa; m.invV = invV; m.inv_rxz = inv_rxz; m.ida = ida; m.sb = sb;
+  m.qbar = qbar; m.alpha = alpha; m.beta = beta; m.qS = qS; m.sgn = sgn; m.sc = sc;
+}
+
+AIRC_HD void f_jac_tail(const DevConst& P, const float v[3], const float q[4], const float w[3], const Ctl& c,
+                        const JacMid& m, float* r) {
+  const float* M = m.M;
+  const float* vbr = m.vbr;
+  const float* vb = m.vb;
+  const float* C = m.C;
+  const float* F = m.F;
+  const float* lq = m.lq;
+  const float* acc = m.acc;
+  const float* Iw = m.Iw;
+  const float inv = m.inv, xa = m.xa, invV = m.invV, inv_rxz = m.inv_rxz, ida = m.ida, sb = m.sb;
+  const float alpha = m.alpha, beta = m.beta, qS = m.qS, sgn = m.sgn, sc = m.sc;
   // ---- D = d v_b / d(v, q):  u = M^T v = (w^2-|qv|^2) v + 2 qv (qv.v) - 2 w (qv x v)
   float D[3][7];
 #pragma unroll
@@ -138,10 +279,9 @@ AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const 
     }
   }
 
-  // ---- surrogate and its Jacobian                                    models.py:143-155, coefficient_models.py:99-104
-  float C[6], J[6][5];
-  surrogate<true>(P.net, qbar, alpha, beta, c, C, J);
-  C[5] = fmaf(P.k_rudder, c.dr, C[5]);
+  // ---- surrogate, derivative pass
+  float J[6][5];
+  surrogate_jac(P.net, m.rr, J);
   if (P.stall_scaling) {                                              // aircraft.py:280-294
     const float k = 10.0f, a30 = 0.52359877559f;
     const float sa = 1.0f / (1.0f + expf(k * (fabsf(alpha) - a30)));
@@ -151,46 +291,9 @@ AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const 
     const float s2 = sa * sbs;
 #pragma unroll
     for (int i = 0; i < 5; ++i) { J[2][i] *= s2; J[4][i] *= sa; }
-    J[2][1] = fmaf(C[2] * sbs, ca, J[2][1]);
-    J[2][2] = fmaf(C[2] * sa, cb, J[2][2]);
-    J[4][1] = fmaf(C[4], ca, J[4][1]);
-    C[2] *= s2;
-    C[4] *= sa;
-  }
-  C[0] = fmaf(P.k_flap_x, c.df, C[0]);                                // aircraft.py:297-299
-  C[2] = fmaf(P.k_flap_z, c.df, C[2]);
-
-  // ---- forces, moments, f                                            aircraft.py:313-328 ; base.py:255-297,344-383
-  const float qS = qbar * P.S;
-  const float sgn = sign_casadi(vb[0]);
-  const float F[3] = {C[0] * qS * sgn, C[1] * qS, C[2] * qS};
-  const float lq[3] = {qbar * P.Sb, qbar * P.Sc, qbar * P.Sb};
-  float Mo[3];
-  Mo[0] = C[3] * lq[0] + (P.com[1] * F[2] - P.com[2] * F[1]);
-  Mo[1] = C[4] * lq[1] + (P.com[2] * F[0] - P.com[0] * F[2]);
-  Mo[2] = C[5] * lq[2] + (P.com[0] * F[1] - P.com[1] * F[0]);
-  const float sc = inv * P.inv_mass;
-  float acc[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    float a = M[3 * i] * F[0];
-    a = fmaf(M[3 * i + 1], F[1], a);
-    a = fmaf(M[3 * i + 2], F[2], a);
-    acc[i] = a * sc;
-    kv[i] = acc[i] + P.g[i];
-  }
-  kq[0] = 0.5f * (q[3] * w[0] + (q[1] * w[2] - q[2] * w[1]));
-  kq[1] = 0.5f * (q[3] * w[1] + (q[2] * w[0] - q[0] * w[2]));
-  kq[2] = 0.5f * (q[3] * w[2] + (q[0] * w[1] - q[1] * w[0]));
-  kq[3] = -0.5f * (q[0] * w[0] + q[1] * w[1] + q[2] * w[2]);
-  float Iw[3];
-#pragma unroll
-  for (int i = 0; i < 3; ++i) Iw[i] = fmaf(P.I[3 * i + 2], w[2], fmaf(P.I[3 * i + 1], w[1], P.I[3 * i] * w[0]));
-  {
-    const float t[3] = {Mo[0] - (w[1] * Iw[2] - w[2] * Iw[1]), Mo[1] - (w[2] * Iw[0] - w[0] * Iw[2]),
-                        Mo[2] - (w[0] * Iw[1] - w[1] * Iw[0])};
-#pragma unroll
-    for (int i = 0; i < 3; ++i) kw[i] = fmaf(P.Iinv[3 * i + 2], t[2], fmaf(P.Iinv[3 * i + 1], t[1], P.Iinv[3 * i] * t[0]));
+    J[2][1] = fmaf(m.Craw2 * sbs, ca, J[2][1]);
+    J[2][2] = fmaf(m.Craw2 * sa, cb, J[2][2]);
+    J[4][1] = fmaf(m.Craw4, ca, J[4][1]);
   }
 
   // ---- Z = d(F, m)/d(qbar, alpha, beta);  F_k = sigma_k qS C_k,  m_k = l_k qbar C_{3+k}
@@ -290,6 +393,13 @@ AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const 
   for (int i = 0; i < 4; ++i) r[JR_Q + i] = q[i];
 #pragma unroll
   for (int i = 0; i < 3; ++i) r[JR_W + i] = w[i];
+}
+
+AIRC_HD void f_jac(const DevConst& P, const float v[3], const float q[4], const float w[3], const Ctl& c,
+                   float kv[3], float kq[4], float kw[3], float* r) {
+  JacMid m;
+  f_jac_head(P, v, q, w, c, kv, kq, kw, m);
+  f_jac_tail(P, v, q, w, c, m, r);
 }
 
 // Phase 1 for one node: the primal RK4 step (x is advanced, NOT normalised) and the node record `rec`

@@ -1,11 +1,11 @@
 // airc_jac_kernel.cuh -- the tile kernel of K2 (mathematics and design notes: airc_jac.cuh).
 //
 // One block = one tile of NT nodes, 2 NT threads.
-//   phase 1: threads 0 .. NT-1, thread t computes node tile*NT + t (primal RK4, surrogate Jacobian, f_x / f_u
-//            blocks of the four stage points) and parks the node record (348 floats; 380 with the d/d(dt)
-//            column) in shared memory with 128-bit stores; x+ (and the multiple-shooting defect) go straight
-//            to global memory.  Phase 1 needs ~250 registers per thread and its records fill the shared
-//            memory, so NT = 128 nodes per SM is what fits; the second half of the block only joins for
+//   phase 1: all 2 NT threads; threads t and t + NT share node tile*NT + t and alternate its RK4 stages (head =
+//            primal k, handed to the partner through shared memory; tail = the f_x / f_u blocks of the stage point,
+//            parked in the node record: 348 floats, 380 with the d/d(dt) column, 128-bit stores); x+ (and the
+//            multiple-shooting defect) go straight to global memory.  The code needs ~250 registers per thread and
+//            the records fill the shared memory, so NT = 128 nodes and 8 warps per SM is what fits.
 //   phase 2: 4 passes of NP = NT/4 nodes; in a pass every group of 8 lanes runs the tangent recursion of one
 //            node (one packed column pair per lane), drops its 13 x 2 results into a shared-memory IMAGE of
 //            the pass's output (A, B, dPhi/ddt in the caller's layout; the constant columns dPhi/dp = [I;0]
@@ -34,6 +34,7 @@ struct JacTile {
   static constexpr int OFF_D = SOA ? 260 * NPS : 260 * NP;
   static constexpr size_t SMEM = (size_t)(NT * JRec<DT>::NODE + IMG) * sizeof(float);
   static_assert(NP % 4 == 0 && (TPB / (NP / 4)) == 32, "write-out mapping");
+  static_assert(2 * 23 * NT <= IMG, "phase 1's exchange area aliases the image");
 };
 
 // full-pass write-out, SoA: E elements x NP nodes; thread -> (element e0 + 32 k, 16-byte chunk `part`)
@@ -64,41 +65,91 @@ AIRC_D void jk_out_lin(float* __restrict__ g, const float* __restrict__ im, int 
     if (tid + k * TPB < COUNT4) reinterpret_cast<float4*>(g)[tid + k * TPB] = v[k];
 }
 
-template <int NT, bool SOA, bool DT>
-__global__ void __launch_bounds__(2 * NT, (NT == 128) ? 1 : ((NT == 64) ? 2 : 4))
-linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const int vec_ok) {
-  using T = JacTile<NT, SOA, DT>;
+// ------------------------------------------------------------------ phase 1: TWO warps per 32 nodes
+// Thread t and thread t + NT work on the same node and alternate the RK4 stages (t: stages 1 and 3, t + NT: 2 and
+// 4).  f_jac_head delivers the primal k after a quarter of a stage's work; the thread then hands the next stage
+// point (and the running RK4 sums) to its partner through shared memory and assembles its Jacobian blocks
+// (f_jac_tail) WHILE the partner already runs the next stage's head: both warps of a pair sit on the same
+// scheduler, so the lone-warp dependency stalls of one fill with the other's instructions.  Hand-over = a named
+// barrier per warp pair and direction (producer bar.arrive, consumer bar.sync, 64 threads); the exchange area
+// aliases the output image, which phase 2 initialises afterwards.
+template <int NT, bool DT>
+AIRC_D void jk_phase1(const DevConst& P, const LinArgs& a, long long node0, int tid, float* __restrict__ recs,
+                      float* __restrict__ xch, int bar0) {
   using L = JRec<DT>;
-  extern __shared__ float4 jk_smem4[];
-  float* const recs = reinterpret_cast<float*>(jk_smem4);
-  float* const img = recs + NT * L::NODE;
-  float* const imgB = img + T::OFF_B;
-  float* const imgD = img + T::OFF_D;
-  const int tid = threadIdx.x;
-  const long long node0 = (long long)blockIdx.x * NT;
-
-  // ---- the constant columns of the image, once per block: dPhi/dp = [I;0] (f does not read p) and
-  //      dPhi/d(thrust) = 0 (thrust is inert, aircraft.py:320)
-  for (int i = tid; i < T::NP * 39; i += T::TPB) {
-    const int j = i / 39, rem = i - j * 39, r = rem / 3, cc = rem - r * 3;
-    if (SOA) {
-      img[(r * 13 + cc) * T::NPS + j] = (r == cc) ? 1.0f : 0.0f;
-      imgB[(r * 7 + 3 + cc) * T::NPS + j] = 0.0f;
-    } else {
-      img[j * 169 + r * 13 + cc] = (r == cc) ? 1.0f : 0.0f;
-      imgB[j * 91 + r * 7 + 3 + cc] = 0.0f;
-    }
+  constexpr int WP = NT / 32;                          // warp pairs
+  const int pnode = tid & (NT - 1), half = tid / NT, pw = (tid >> 5) & (WP - 1);
+  const long long node = node0 + pnode;
+  const bool live = node < a.n;
+  float* const rec = recs + pnode * L::NODE;
+  const int bar_ab = bar0 + pw, bar_ba = bar0 + WP + pw;     // first half -> second half, and back
+  State s;
+  Ctl c = {};
+  float dt = 0.0f;
+  if (live) {
+    load_state(a.x, node, s);
+    c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
+    dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
   }
-
-  // ------------------------------------------------------------------ phase 1: one node per thread
-  if (tid < NT) {
-    const long long node = node0 + tid;
-    if (node < a.n) {
-      State s;
-      load_state(a.x, node, s);
-      const Ctl c = load_ctl(a.u.base + node * a.u.sb, a.u.sc);
-      const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
-      jac_phase1<DT>(P, s, c, dt, recs + tid * L::NODE);
+  const float hh = 0.5f * dt, h6 = dt * (1.0f / 6.0f);
+  float sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
+#pragma unroll 1
+  for (int it = 0; it < 2; ++it) {
+    const int stage = 2 * it + half;
+    const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
+    const float cn = (stage == 2) ? dt : hh;
+    // ---- receive the stage point and the sums so far
+    if (stage == 0) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) { sv[i] = s.v[i]; sw[i] = s.w[i]; ap[i] = av[i] = aw[i] = 0.0f; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { sq[i] = s.q[i]; aq[i] = 0.0f; }
+    } else {
+      asm volatile("bar.sync %0, 64;" :: "r"(half ? bar_ab : bar_ba) : "memory");
+      const float* mi = xch + (half ? 0 : 23 * NT) + pnode;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        sv[i] = mi[i * NT]; sw[i] = mi[(7 + i) * NT];
+        ap[i] = mi[(10 + i) * NT]; av[i] = mi[(13 + i) * NT]; aw[i] = mi[(20 + i) * NT];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { sq[i] = mi[(3 + i) * NT]; aq[i] = mi[(16 + i) * NT]; }
+    }
+    // ---- head: k = f(X_stage)
+    float kv[3], kq[4], kw[3];
+    JacMid m;
+    if (live) f_jac_head(P, sv, sq, sw, c, kv, kq, kw, m);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      ap[i] = fmaf(wgt, sv[i], ap[i]);
+      av[i] = fmaf(wgt, kv[i], av[i]);
+      aw[i] = fmaf(wgt, kw[i], aw[i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) aq[i] = fmaf(wgt, kq[i], aq[i]);
+    // ---- hand over (stages 1..3), or finish the step (stage 4)
+    if (stage < 3) {
+      float* mo = xch + (half ? 23 * NT : 0) + pnode;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        mo[i * NT] = fmaf(cn, kv[i], s.v[i]); mo[(7 + i) * NT] = fmaf(cn, kw[i], s.w[i]);
+        mo[(10 + i) * NT] = ap[i]; mo[(13 + i) * NT] = av[i]; mo[(20 + i) * NT] = aw[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { mo[(3 + i) * NT] = fmaf(cn, kq[i], s.q[i]); mo[(16 + i) * NT] = aq[i]; }
+      asm volatile("bar.arrive %0, 64;" :: "r"(half ? bar_ba : bar_ab) : "memory");
+    } else if (live) {
+      Q4* hd = reinterpret_cast<Q4*>(rec + L::HDR);
+      hd[0] = Q4{dt, ap[0], ap[1], ap[2]};
+      hd[1] = Q4{aq[0], aq[1], aq[2], aq[3]};
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        s.p[i] = fmaf(h6, ap[i], s.p[i]);
+        s.v[i] = fmaf(h6, av[i], s.v[i]);
+        s.w[i] = fmaf(h6, aw[i], s.w[i]);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) s.q[i] = fmaf(h6, aq[i], s.q[i]);
       if (a.normalise) normalise_q<0>(s, nullptr);
       if (a.xn.base) store_state(a.xn, node, s);
       if (a.r.base) {
@@ -111,8 +162,46 @@ linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const
         store_state(a.r, node, t);
       }
     }
+    // ---- tail: the Jacobian blocks of this stage point -> node record
+    if (live) {
+      float r[92];
+      r[82] = r[83] = 0.0f;
+      f_jac_tail(P, sv, sq, sw, c, m, r);
+      if (DT) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) { r[JR_K + i] = kv[i]; r[JR_K + 7 + i] = kw[i]; }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) r[JR_K + 3 + i] = kq[i];
+      }
+      Q4* dst = reinterpret_cast<Q4*>(rec + stage * L::STAGE);
+#pragma unroll
+      for (int i = 0; i < L::STAGE / 4; ++i) dst[i] = Q4{r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]};
+    }
   }
-  __syncthreads();
+}
+
+// Phase 2 for the NT nodes whose records are in `recs`, by 2 NT threads (tid 0 .. 2 NT - 1); `sync` is the barrier
+// of exactly those threads.
+template <int NT, bool SOA, bool DT, class Sync>
+AIRC_D void jk_phase2(const LinArgs& a, long long node0, int tid, const float* __restrict__ recs, float* __restrict__ img,
+                      int vec_ok, Sync sync) {
+  using T = JacTile<NT, SOA, DT>;
+  using L = JRec<DT>;
+  constexpr int TPB2 = T::TPB;
+  float* const imgB = img + T::OFF_B;
+  float* const imgD = img + T::OFF_D;
+  // ---- the constant columns of the image, once per block: dPhi/dp = [I;0] (f does not read p) and
+  //      dPhi/d(thrust) = 0 (thrust is inert, aircraft.py:320)
+  for (int i = tid; i < T::NP * 39; i += TPB2) {
+    const int j = i / 39, rem = i - j * 39, r = rem / 3, cc = rem - r * 3;
+    if (SOA) {
+      img[(r * 13 + cc) * T::NPS + j] = (r == cc) ? 1.0f : 0.0f;
+      imgB[(r * 7 + 3 + cc) * T::NPS + j] = 0.0f;
+    } else {
+      img[j * 169 + r * 13 + cc] = (r == cc) ? 1.0f : 0.0f;
+      imgB[j * 91 + r * 7 + 3 + cc] = 0.0f;
+    }
+  }
 
   // ------------------------------------------------------------------ phase 2: eight lanes per node
   const int lane8 = tid & 7, grp = tid >> 3;
@@ -147,7 +236,7 @@ linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const
         if (has_hi) *oh = col[r].hi;
       }
     }
-    __syncthreads();
+    sync();
     // ---- stream the image out
     const long long left = a.n - pnode0;
     const int m = left < T::NP ? (int)left : T::NP;    // valid nodes of this pass
@@ -160,7 +249,7 @@ linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const
       } else {
         auto out = [&](float* g, const float* im, int E) {
           if (!g) return;
-          for (int i = tid; i < E * T::NP; i += T::TPB) {
+          for (int i = tid; i < E * T::NP; i += TPB2) {
             const int e = i / T::NP, j = i - e * T::NP;
             if (j < m) g[(long long)e * a.n + pnode0 + j] = im[e * T::NPS + j];
           }
@@ -171,21 +260,36 @@ linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const
       }
     } else {
       if (vec_ok && m == T::NP) {                        // 16-byte aligned bases; pnode0 % 4 == 0 by construction
-        if (a.A) jk_out_lin<T::NP * 169 / 4, T::TPB>(a.A + pnode0 * 169, img, tid);
-        if (a.Bm) jk_out_lin<T::NP * 91 / 4, T::TPB>(a.Bm + pnode0 * 91, imgB, tid);
-        if (DT && a.Dt) jk_out_lin<T::NP * 13 / 4, T::TPB>(a.Dt + pnode0 * 13, imgD, tid);
+        if (a.A) jk_out_lin<T::NP * 169 / 4, TPB2>(a.A + pnode0 * 169, img, tid);
+        if (a.Bm) jk_out_lin<T::NP * 91 / 4, TPB2>(a.Bm + pnode0 * 91, imgB, tid);
+        if (DT && a.Dt) jk_out_lin<T::NP * 13 / 4, TPB2>(a.Dt + pnode0 * 13, imgD, tid);
       } else {
         auto out = [&](float* g, const float* im, int count) {
           if (!g) return;
-          for (int i = tid; i < count; i += T::TPB) g[i] = im[i];
+          for (int i = tid; i < count; i += TPB2) g[i] = im[i];
         };
         out(a.A ? a.A + pnode0 * 169 : nullptr, img, m * 169);
         out(a.Bm ? a.Bm + pnode0 * 91 : nullptr, imgB, m * 91);
         if (DT) out(a.Dt ? a.Dt + pnode0 * 13 : nullptr, imgD, m * 13);
       }
     }
-    __syncthreads();
+    sync();
   }
+}
+
+template <int NT, bool SOA, bool DT>
+__global__ void __launch_bounds__(2 * NT, (NT == 128) ? 1 : ((NT == 64) ? 2 : 4))
+linearize_tile_kernel(const __grid_constant__ DevConst P, const LinArgs a, const int vec_ok) {
+  using T = JacTile<NT, SOA, DT>;
+  using L = JRec<DT>;
+  extern __shared__ float4 jk_smem4[];
+  float* const recs = reinterpret_cast<float*>(jk_smem4);
+  float* const img = recs + NT * L::NODE;
+  const int tid = threadIdx.x;
+  const long long node0 = (long long)blockIdx.x * NT;
+  jk_phase1<NT, DT>(P, a, node0, tid, recs, img /* the exchange area aliases the image */, 1);
+  __syncthreads();
+  jk_phase2<NT, SOA, DT>(a, node0, tid, recs, img, vec_ok, [] { __syncthreads(); });
 }
 
 }  // namespace airc
