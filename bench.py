@@ -805,13 +805,22 @@ def side_extras(torch, ac, dev, args):
         xt = acd.state_update(xa.T.contiguous(), ua.T.contiguous(), DT).T.contiguous()
         Xw = torch.cat([xa[:1], xt], 0)[None]                    # a [1, 299, 13] guess, U [1, 298, 7]
         t_g = time_launches(torch, lambda: acd.state_update(xa.T, ua.T, DT), max(K, 20), 3, flush)
-        t_j = time_launches(torch, lambda: acd.defects(Xw, ua[None], DT), max(K, 20), 3, flush)
+        t_jf = time_launches(torch, lambda: acd.defects(Xw, ua[None], DT), max(K, 20), 3, flush)
+        # the same blocks through the C ABI on prepared buffers (the facade call above also slices / copies X into
+        # x_k, x_{k+1}: three small torch kernels and their launch latency)
+        from aircraft_b200 import _cabi as _cb
+        rj, Aj, Bj = torch.empty_like(xa), torch.empty(nn_, 13, 13, device=dev), torch.empty(nn_, 13, 7, device=dev)
+        stj = torch.cuda.current_stream().cuda_stream
+        t_j = time_launches(torch, lambda: acd._lib.airc_defects(
+            acd.handle, xa.data_ptr(), ua.data_ptr(), xt.data_ptr(), DT, None, nn_, 1, 1, _cb.LAYOUT_AOS, rj.data_ptr(),
+            Aj.data_ptr(), Bj.data_ptr(), None, stj), max(K, 20), 3, flush)
         t_h = time_launches(torch, lambda: acd.lagrangian_hessian(xa, ua, la, DT), max(K, 20), 3, flush)
         out["mpc_blocks_default_298"] = {
             "workload": "298 shooting nodes, DEFAULT coefficient model, 1 substep: the dynamics blocks behind IPOPT's "
                         "nlp_g / nlp_jac_g / nlp_hess_l callbacks (values, defect Jacobian blocks A B, exact Hessian blocks)",
             "unit": "ms per evaluation", "higher_is_better": False,
-            "state_update_ms": t_g, "defects_with_jacobian_blocks_ms": t_j, "lagrangian_hessian_ms": t_h,
+            "state_update_ms": t_g, "defects_with_jacobian_blocks_ms": t_j, "defects_through_facade_ms": t_jf,
+            "lagrangian_hessian_ms": t_h,
             "reference_published": {"nlp_g_ms": 0.65752, "nlp_jac_g_ms": 14.24, "nlp_hess_l_ms": 55.79,
                                     "source": "reference todo.md:38 via BASELINE.md section 2 (unknown CPU, 1 thread; whole-NLP "
                                               "callbacks incl. non-dynamics constraints: context, not a like-for-like ratio)"},
