@@ -300,12 +300,9 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
     const bool soa = layout == AIRC_LAYOUT_SOA, want_dt = Dt != nullptr;
     auto al16 = [](const void* p) { return p == nullptr || ((uintptr_t)p & 15u) == 0; };
     const int vec_ok = (al16(A) && al16(Bm) && al16(Dt) && (!soa || (n & 3) == 0)) ? 1 : 0;
-    // tiles of 128 nodes (one block per SM) once every SM has at least two of them; 64-node tiles below that
-#ifdef AIRC_JAC_FORCE_NT            // build-variant A/B only (profiles/build_variants.py); never set in the shipped build
-    const bool big = AIRC_JAC_FORCE_NT == 128;
-#else
-    const bool big = n >= (int64_t)h->sm_count * 256;
-#endif
+    // Tile size (profiles/r2_variants_linearize.txt): 64 nodes per block, two blocks per SM -- one block's tangent
+    // recursion and write-out overlap the other's assembly phase; AoS without the d/d(dt) column runs 32-node tiles
+    // (four blocks per SM; in SoA their 32-byte row segments cost more than the extra overlap gives).
 #define AIRC_JAC_LAUNCH(NT_, SOA_, DT_)                                                                     \
     do {                                                                                                    \
       using T_ = JacTile<NT_, SOA_, DT_>;                                                                   \
@@ -320,10 +317,10 @@ static int linearize_impl(const AircHandle* h, const float* x, const float* u, f
       else if (want_dt) AIRC_JAC_LAUNCH(NT_, false, true);                                                  \
       else AIRC_JAC_LAUNCH(NT_, false, false);                                                              \
     } while (0)
-#if defined(AIRC_JAC_FORCE_NT) && AIRC_JAC_FORCE_NT == 32
-    AIRC_JAC_PICK(32);
+#if defined(AIRC_JAC_FORCE_NT)       // build-variant A/B only (profiles/build_variants.py); never set in the shipped build
+    AIRC_JAC_PICK(AIRC_JAC_FORCE_NT);
 #else
-    if (big) AIRC_JAC_PICK(128);
+    if (!soa && !want_dt) AIRC_JAC_LAUNCH(32, false, false);
     else AIRC_JAC_PICK(64);
 #endif
 #undef AIRC_JAC_PICK

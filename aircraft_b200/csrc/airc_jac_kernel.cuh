@@ -12,8 +12,8 @@
 //            and dPhi/d(thrust) = 0 are written into the image once per block), and the whole block streams
 //            the image out with 128-bit stores: AoS -- NP x 169 (91, 13) contiguous floats; SoA -- one
 //            16-byte chunk = four consecutive nodes of one matrix element.
-// Shared memory (NT = 128): 174 KB of records + 33..37 KB of image, one block (8 warps) per SM; NT = 64: two
-// blocks per SM (small problems: more blocks to spread over the SMs).
+// Shared memory: NT = 64 (shipped for SoA and d/d(dt)): 87 KB of records + 17..21 KB of image, two blocks per SM;
+// NT = 32 (shipped for AoS): four blocks per SM; NT = 128: one block per SM (A/B variant only).
 #pragma once
 #include "airc_jac.cuh"
 #include "airc_kernels.cuh"
