@@ -276,10 +276,12 @@ def test_sweep_equals_packed_explicit_rollout(ac_packed, x0):
     assert torch.equal(e.trajectory[:, :, am], r.trajectory)
 
 
-def test_nan_in_the_nominal_sequence_propagates(ac, x0):
+@pytest.mark.parametrize("B", [300, 125000])          # FFMA2 sweep kernel / tensor-core sweep kernel
+def test_nan_in_the_nominal_sequence_propagates(ac, x0, B):
     """The sampler's clamp keeps NaN (min.NaN / max.NaN): a NaN in U_nom makes every candidate's cost NaN instead of
-    silently sampling around the lower actuator limit."""
-    B, H = 300, 12
+    silently sampling around the lower actuator limit.  On the tensor-core kernel the NaN also has to survive the
+    TF32 operand split, the MMAs and the clamped logistic."""
+    H = 12
     Un = nominal(H)
     Un[5, 1] = np.nan
     r = ac.sweep(f32(x0), f32(Un), DT, B, sampler=make_sweep_params(seed=4), return_costs=True)
@@ -304,3 +306,30 @@ def test_sweep_plan_graph_replay_equals_eager_sweep(ac, x0):
         want = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
         assert torch.equal(got.raw, want.raw) and torch.equal(got.cost, want.cost)
         assert int(got.argmin) == int(want.argmin)
+
+
+def test_tensor_core_sweep_against_ffma2_sweep_and_nan_state(ac, x0):
+    """The same candidates through both sweep kernels: a shard just above the tensor-core threshold and the same
+    shard cut in two halves below it (FFMA2 kernel; the sampler is keyed on the global index).  Costs agree to the
+    parity bar, the arg-min is the same candidate unless the two best are closer than that.  A NaN initial state
+    makes every cost NaN on the tensor path too."""
+    sm = torch.cuda.get_device_properties(0).multi_processor_count
+    B, H = 3 * 256 * sm + 64, 20
+    Un = nominal(H)
+    sp, cp = make_sweep_params(seed=77), make_cost_params()
+    whole = ac.sweep(f32(x0), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True)
+    half = B // 2
+    sp2 = make_sweep_params(seed=77, index_offset=half)
+    a = ac.sweep(f32(x0), f32(Un), DT, half, sampler=sp, cost=cp, return_costs=True)
+    b = ac.sweep(f32(x0), f32(Un), DT, B - half, sampler=sp2, cost=cp, return_costs=True)
+    parts = torch.cat([a.cost, b.cost])
+    assert torch.isfinite(whole.cost).all()
+    err = float((whole.cost - parts).abs().max() / parts.abs().max())
+    print(f"tensor-core sweep vs FFMA2 sweep, {B} x {H}: max cost difference {err:.2e} of the largest cost")
+    assert err < 1e-5
+    order = torch.sort(parts).values
+    if float(order[1] - order[0]) > 2e-5 * float(order[0].abs()):
+        assert int(whole.argmin) == int(torch.argmin(parts))
+    xb = x0.copy()
+    xb[4] = np.nan
+    assert torch.isnan(ac.sweep(f32(xb), f32(Un), DT, B, sampler=sp, cost=cp, return_costs=True).cost).all()
