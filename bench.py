@@ -838,6 +838,19 @@ def side_extras(torch, ac, dev, args):
                      "value": nh / (ms * 1e-3), "unit": "hessian-evals/s", "ms_per_launch": ms,
                      "l2": "flushed between launches",
                      "reference_context": "nlp_hess_l 56-560 ms per IPOPT iteration at 298 nodes (reference todo.md tables, CPU)"}
+        aud = kernel_audit("hessian")
+        if aud and name == "hessian_bulk":
+            ex, by = aud["executed_fp32_flops_per_unit"], aud["dram_bytes_per_unit"]
+            tf = nh * ex / (ms * 1e-3) / 1e12
+            pk = fp32_peak(ac)
+            out[name]["roofline"] = {
+                "kernel": "hessian_kernel<soa> (second-order forward mode on jets, 64 threads per node)", "bound": "fp32",
+                "achieved": tf, "peak": pk, "unit": "TFLOP/s", "frac": tf / pk,
+                "executed_flops_per_eval": ex, "dram_bytes_per_eval": by,
+                "algorithmic_bytes_per_eval": 4 * (13 + 7 + 13 + 441 + 21),
+                "source": f"profiles/{aud['capture']} via profiles/r2_kernel_audit.json (EXECUTED flops: this kernel re-evaluates "
+                          f"the value and outer-direction parts in every thread, so executed work overstates the useful "
+                          f"work ~3x); CUDA sources {'CHANGED since' if aud['stale'] else 'unchanged since'} the capture"}
     return out
 
 
