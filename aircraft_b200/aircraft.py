@@ -458,9 +458,9 @@ class Aircraft:
                       (batch index fastest: the kernels' native, fully coalesced layout)
         cost: None, True (default weights), a dict of make_cost_params kwargs or an
               AircCostParams -> per-trajectory primary MPC loss (main/control/control.py:35-70).
-        cooperative: latency mode ('nn' model): 8 lanes share one trajectory.  The library picks it by itself for
-              B <= 32 x SM count; this flag (AIRC_FLAG_COOPERATIVE) extends it to B <= 64 x SM count.  Last-bit
-              differences from the one-trajectory-per-thread kernel.
+        cooperative: latency mode ('nn' model): 8 / 4 / 2 lanes share one trajectory (by batch size).  The library picks
+              it by itself for B <= 32 x SM count; this flag (AIRC_FLAG_COOPERATIVE) extends it to B <= 64 x SM
+              count.  Last-bit differences between the kernel instantiations.
         packed: run the two-trajectories-per-thread kernel (the sweep's arithmetic, AIRC_FLAG_PACKED) whatever the
               batch size; by default it serves batches of two waves and more.
         """

@@ -238,17 +238,30 @@ int airc_rollout(const AircHandle* h, const float* x0, const float* U, float dt,
     else rollout_kernel<false, false, 1><<<grid, bs, 0, st>>>(h->dc, a);
     return check_launch();
   }
-  // small batches (latency case, configs 1 and 2): 8 lanes per trajectory (airc_coop.cuh).  The default while the
-  // batch leaves SM sub-partitions idle on the one-trajectory kernel (B <= 32 x SM count); AIRC_FLAG_COOPERATIVE
-  // extends it to 64 x SM count.  4 / 2 lanes and a packed-pair variant measured slower at every size
-  // (profiles/r2_variants_latency.txt).
+  // small batches (latency case, configs 1 and 2): 8, 4 or 2 lanes share one trajectory (airc_coop.cuh) -- as many as
+  // keep the batch at ONE warp per SM sub-partition (B <= 16 / 32 / 64 x SM count): the launch is bound by each warp's
+  // dependency chain, and a second warp on a scheduler costs more than the longer chain of fewer lanes.  The default
+  // while the batch leaves sub-partitions idle on the one-trajectory kernel (B <= 32 x SM count);
+  // AIRC_FLAG_COOPERATIVE extends it to 64 x SM count (profiles/r2_variants_latency.txt).
   if (h->packed == 1 && !(flags & AIRC_FLAG_PACKED) &&
       (B <= (long long)h->sm_count * 32 || ((flags & AIRC_FLAG_COOPERATIVE) && B <= (long long)h->sm_count * 64))) {
-    const unsigned gridc = (unsigned)((B * 8 + 127) / 128);
-    if (cost && X) rollout_coop_kernel<true, true, 8><<<gridc, 128, 0, st>>>(h->dc, a);
-    else if (cost) rollout_coop_kernel<true, false, 8><<<gridc, 128, 0, st>>>(h->dc, a);
-    else if (X) rollout_coop_kernel<false, true, 8><<<gridc, 128, 0, st>>>(h->dc, a);
-    else rollout_coop_kernel<false, false, 8><<<gridc, 128, 0, st>>>(h->dc, a);
+#ifndef AIRC_AB_COOP_LANES          // build-variant A/B only: 0 = lanes by batch size (shipped), 2 / 4 / 8 = fixed
+#define AIRC_AB_COOP_LANES 0
+#endif
+    const long long slots = (long long)h->sm_count * 128;          // threads of one warp per sub-partition
+    const int Lc = AIRC_AB_COOP_LANES ? AIRC_AB_COOP_LANES : (B * 8 <= slots ? 8 : (B * 4 <= slots ? 4 : 2));
+    const unsigned gridc = (unsigned)((B * Lc + 127) / 128);
+#define AIRC_COOP_LAUNCH(LL)                                                                             \
+    do {                                                                                                 \
+      if (cost && X) rollout_coop_kernel<true, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);              \
+      else if (cost) rollout_coop_kernel<true, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);             \
+      else if (X) rollout_coop_kernel<false, true, LL><<<gridc, 128, 0, st>>>(h->dc, a);                \
+      else rollout_coop_kernel<false, false, LL><<<gridc, 128, 0, st>>>(h->dc, a);                      \
+    } while (0)
+    if (Lc == 8) AIRC_COOP_LAUNCH(8);
+    else if (Lc == 4) AIRC_COOP_LAUNCH(4);
+    else AIRC_COOP_LAUNCH(2);
+#undef AIRC_COOP_LAUNCH
     return check_launch();
   }
   if (h->packed == 2 || (h->packed == 1 && ((flags & AIRC_FLAG_PACKED) || B >= 2 * wave2))) {

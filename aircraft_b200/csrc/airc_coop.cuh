@@ -143,8 +143,9 @@ struct NetCoop {
 
 // Primal RK4 step with the network evaluated through a policy (NetCoop: shared by the lanes of a group).
 // Same arithmetic as rk4_step<0> apart from the network's summation order.
+// speed2 (optional) receives |v_b|^2 of the step's first stage point, i.e. of the node itself (the loss's speed term).
 template <class Net>
-AIRC_HD void rk4_step_net(const DevConst& P, const Net& net, State& x, const Ctl& c, float h) {
+AIRC_HD void rk4_step_net(const DevConst& P, const Net& net, State& x, const Ctl& c, float h, float* speed2 = nullptr) {
   const float hh = 0.5f * h, h6 = h * (1.0f / 6.0f);
   float sv[3], sq[4], sw[3], ap[3], av[3], aq[4], aw[3];
 #pragma unroll
@@ -159,6 +160,7 @@ AIRC_HD void rk4_step_net(const DevConst& P, const Net& net, State& x, const Ctl
     Stage st;
     float J[6][5];
     f_eval_net<false>(P, net, sv, sq, sw, c, kv, kq, kw, st, J);
+    if (stage == 0 && speed2) *speed2 = fmaf(st.vb[2], st.vb[2], fmaf(st.vb[1], st.vb[1], st.vb[0] * st.vb[0]));
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
       ap[i] = fmaf(wgt, sv[i], ap[i]);
@@ -185,9 +187,10 @@ AIRC_HD void rk4_step_net(const DevConst& P, const Net& net, State& x, const Ctl
 
 template <class Net>
 AIRC_HD void state_update_net(const DevConst& P, const Net& net, State& x, const Ctl& c, float dt, int substeps,
-                              bool normalise) {
+                              bool normalise, float* speed2 = nullptr) {
   const float h = (substeps == 1) ? dt : dt / (float)substeps;
-  for (int s = 0; s < substeps; ++s) rk4_step_net(P, net, x, c, h);
+  rk4_step_net(P, net, x, c, h, speed2);
+  for (int s = 1; s < substeps; ++s) rk4_step_net(P, net, x, c, h);
   if (normalise) normalise_q<0>(x, nullptr);
 }
 

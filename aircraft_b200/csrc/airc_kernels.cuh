@@ -279,15 +279,34 @@ rollout_coop_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
   const NetCoop<L> net{&snet, lane};
   float sum_du = 0.0f, sum_v2 = 0.0f;
   float up[7];
+  // The controls of step k + 1 are fetched BEFORE step k is integrated: in this kernel nothing else hides the
+  // global-memory latency (one or two warps per scheduler), and it would otherwise start every step.
+  Ctl cn = {};
+  float tn[3] = {0.0f, 0.0f, 0.0f};
+  if (a.H > 0) {
+    cn = load_ctl(u, a.u_sc);
+    if (COST) {
+#pragma unroll
+      for (int i = 0; i < 3; ++i) tn[i] = __ldg(u + (3 + i) * a.u_sc);
+    }
+  }
 #pragma unroll 1
   for (int k = 0; k < a.H; ++k) {
-    const float* uk = u + k * a.u_sk;
-    const Ctl c = load_ctl(uk, a.u_sc);
+    const Ctl c = cn;
+    const float t3[3] = {tn[0], tn[1], tn[2]};
+    if (k + 1 < a.H) {
+      const float* un1 = u + (long long)(k + 1) * a.u_sk;
+      cn = load_ctl(un1, a.u_sc);
+      if (COST) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) tn[i] = __ldg(un1 + (3 + i) * a.u_sc);
+      }
+    }
     if (COST) {
       float un[7];
       un[0] = c.da; un[1] = c.de; un[2] = c.dr; un[6] = c.df;
 #pragma unroll
-      for (int i = 3; i < 6; ++i) un[i] = __ldg(uk + i * a.u_sc);
+      for (int i = 3; i < 6; ++i) un[i] = t3[i - 3];
       if (k > 0) {
 #pragma unroll
         for (int i = 0; i < 7; ++i) {
@@ -297,9 +316,10 @@ rollout_coop_kernel(const __grid_constant__ DevConst P, const RolloutArgs a) {
       }
 #pragma unroll
       for (int i = 0; i < 7; ++i) up[i] = un[i];
-      sum_v2 += body_speed2(P, s);
     }
-    state_update_net(P, net, s, c, a.dt, a.substeps, a.normalise != 0);
+    float sp2 = 0.0f;
+    state_update_net(P, net, s, c, a.dt, a.substeps, a.normalise != 0, COST ? &sp2 : nullptr);
+    if (COST) sum_v2 += sp2;
     if (TRAJ && writer) store_state(VecViewW{Xb + (long long)(k + 1) * a.X_sk, 0, a.X_sc}, 0, s);
   }
   if (!writer) return;

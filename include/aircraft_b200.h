@@ -54,12 +54,13 @@ extern "C" {
 /* flags */
 #define AIRC_FLAG_NORMALISE 1u   /* q <- q/|q| as base.py:443-444 / :473-474 (opts['quaternion']=='integration') */
 #define AIRC_FLAG_SHARED_U  2u   /* rollout: U is one [H][7] sequence shared by all trajectories */
-#define AIRC_FLAG_COOPERATIVE 4u /* rollout, 'nn' model: latency mode -- 8 lanes share one trajectory (the network's
-                                  * hidden units are split among them).  It is the DEFAULT for B <= 32 x SM count (the
-                                  * batch would leave sub-partitions idle on the one-trajectory kernel); this flag
-                                  * extends it to B <= 64 x SM count.  Results differ from the one-trajectory kernel in
-                                  * the last bits (different summation order): a sharded batch is bit-identical to the
-                                  * whole one only while both run the same kernel. */
+#define AIRC_FLAG_COOPERATIVE 4u /* rollout, 'nn' model: latency mode -- 8, 4 or 2 lanes share one trajectory (the network's
+                                  * hidden units are split among them; as many lanes as keep the batch at one warp per
+                                  * SM sub-partition: B <= 16 / 32 / 64 x SM count).  It is the DEFAULT for B <= 32 x SM
+                                  * count (the batch would leave sub-partitions idle on the one-trajectory kernel);
+                                  * this flag extends it to B <= 64 x SM count.  Kernel instantiations differ in the
+                                  * last bits (summation order, contraction): a sharded batch is bit-identical to the
+                                  * whole one only while both sides run the same instantiation. */
 
 #define AIRC_FLAG_PACKED 8u      /* rollout, 'nn' model: run the two-trajectories-per-thread kernel (the sweep's arithmetic)
                                   * whatever the batch size; by default it serves batches of two waves and more, where it

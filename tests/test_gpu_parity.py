@@ -232,12 +232,13 @@ def test_diagnostics_side_functions(ac, orc):
 
 
 def test_cooperative_small_batch_rollout(ac, orc):
-    """Latency mode (8 lanes per trajectory; the default dispatch up to 32 x SM count trajectories, up to 64 x SM count
-    under AIRC_FLAG_COOPERATIVE): teacher-forced parity with the oracle at every step, run-to-run determinism,
-    agreement with the other rollout kernels (default dispatch, two-trajectories-per-thread) to rounding."""
+    """Latency mode (8 / 4 / 2 lanes per trajectory by batch size; the default dispatch up to 32 x SM count
+    trajectories, up to 64 x SM count under AIRC_FLAG_COOPERATIVE): teacher-forced parity with the oracle at every
+    step for each lane count, run-to-run determinism, agreement with the other rollout kernels (default dispatch,
+    two-trajectories-per-thread) to rounding."""
     from aircraft_b200.workloads import make_control_sequences
     H = 12
-    for B in (3, 2368, 4000, 9000):                 # 9000: latency mode only under the flag on a 148-SM part
+    for B in (3, 2368, 4000, 9000):                 # 8, 8, 4 and (under the flag only) 2 lanes on a 148-SM part
         x0 = make_states(B, seed=81)
         U = make_control_sequences(B, H, seed=81)
         a = ac.rollout(f32(x0), f32(U), 0.01, normalise=True, return_trajectory=True, cost=True, cooperative=True)
