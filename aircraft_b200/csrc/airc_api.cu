@@ -12,6 +12,7 @@
 #include "airc_kernels2.cuh"
 #include "airc_jac_kernel.cuh"
 #include "airc_hess.cuh"
+#include "airc_hess2.cuh"
 #include "airc_peak.cuh"
 #include "airc_sweep.cuh"
 #include "airc_sweep2.cuh"
@@ -389,6 +390,21 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   a.normalise = (int)(flags & AIRC_FLAG_NORMALISE);
   a.H = H; a.grad = grad; a.value = value;
   const int bs = 128;
+#ifndef AIRC_AB_HESS_JETS          // build-variant A/B only: 1 keeps the network model on the second-order jets too
+#define AIRC_AB_HESS_JETS 0
+#endif
+#ifndef AIRC_AB_HESS_SMALL         // build-variant A/B only: node count per SM up to which the jets kernel runs
+#define AIRC_AB_HESS_SMALL 3
+#endif
+  if (!h->dc.model && substeps <= HESS2_MAXSUB && !AIRC_AB_HESS_JETS && n > (long long)AIRC_AB_HESS_SMALL * h->sm_count) {
+    // the NN surrogate: forward over reverse, eight threads per node (airc_hess2.cuh).  Short horizons (up to
+    // three nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
+    const unsigned grid = (unsigned)((n * HESS2_LANES + bs - 1) / bs);
+    if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
+    else hessian2_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+    return check_launch();
+  }
+  // table models, short horizons, and more substeps than the reverse sweep keeps: second-order jets, 64 threads per node
   const long long threads = n * HESS_LANES;
   const unsigned grid = (unsigned)((threads + bs - 1) / bs);
   if (h->dc.model) {

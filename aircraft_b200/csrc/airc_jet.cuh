@@ -12,12 +12,14 @@
 // The pair arithmetic is FFMA2 (fma.rn.f32x2), value and outer parts are scalar.
 #pragma once
 #include "airc_dynamics.cuh"
+#include "airc_tangent.cuh"
 
 namespace airc {
 
 struct Jet {
   float v, o;
   F2 g, og;
+  static AIRC_HD Jet cst(float c) { return Jet{c, 0.0f, F2{0.0f, 0.0f}, F2{0.0f, 0.0f}}; }
 };
 
 AIRC_HD Jet jconst(float c) { return Jet{c, 0.0f, F2{0.0f, 0.0f}, F2{0.0f, 0.0f}}; }
@@ -104,9 +106,7 @@ AIRC_HD Jet jstall(const Jet& a, float k, float a0) {
   return jchain(a, s, s1 * sg, -k * (1.0f - 2.0f * s) * s1);
 }
 
-struct CtlJ {
-  Jet da, de, dr, df;
-};
+using CtlJ = CtlT<Jet>;   // CtlT: airc_tangent.cuh
 
 // ---- the registry's other coefficient models on jets (the float versions are in airc_alt.cuh)
 // outputs K0..K1-1 of the degree-3 polynomial table at x (sklearn monomial order), without storing the monomials
@@ -180,18 +180,20 @@ AIRC_HD void alt_coefficients_jet(const DevConst& P, const Jet vb[3], const Jet&
 
 // f(x,u) on jets, the same rotation-matrix form as f_eval_net (base.py:385-406); p_dot = v is left
 // to the caller.  MODEL 0: the NN surrogate; 1: the table models of airc_alt.cuh.
-template <int MODEL = 0>
-AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet w[3], const CtlJ& c,
-                   Jet vdot[3], Jet qdot[4], Jet wdot[3]) {
-  const Jet &x = q[0], &y = q[1], &z = q[2], &s = q[3];
-  const Jet xx = x * x, yy = y * y, zz = z * z, ww = s * s;
-  const Jet n2 = (xx + yy) + (zz + ww);
-  Jet M[9];
+// J is the jet type: Jet (second order) or Dual (value + two first-order directions, airc_hess2.cuh); the
+// table models exist on Jet only.
+template <int MODEL = 0, class J = Jet>
+AIRC_HD void f_jet(const DevConst& P, const J v[3], const J q[4], const J w[3], const CtlT<J>& c,
+                   J vdot[3], J qdot[4], J wdot[3]) {
+  const J &x = q[0], &y = q[1], &z = q[2], &s = q[3];
+  const J xx = x * x, yy = y * y, zz = z * z, ww = s * s;
+  const J n2 = (xx + yy) + (zz + ww);
+  J M[9];
   M[0] = (ww + xx) - (yy + zz);
   M[4] = (ww + yy) - (xx + zz);
   M[8] = (ww + zz) - (xx + yy);
   {
-    const Jet xy = x * y, xz = x * z, yz = y * z, wx = s * x, wy = s * y, wz = s * z;
+    const J xy = x * y, xz = x * z, yz = y * z, wx = s * x, wy = s * y, wz = s * z;
     M[1] = 2.0f * (xy - wz);
     M[2] = 2.0f * (xz + wy);
     M[3] = 2.0f * (xy + wz);
@@ -199,32 +201,32 @@ AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet 
     M[6] = 2.0f * (xz - wy);
     M[7] = 2.0f * (yz + wx);
   }
-  const Jet inv_n2 = jrcp(n2);
-  Jet vb[3];
+  const J inv_n2 = jrcp(n2);
+  J vb[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     vb[i] = jmad(M[6 + i], v[2], jmad(M[3 + i], v[1], M[i] * v[0])) * inv_n2 + P.eps;   // base.py:156-159
-  const Jet vb2 = jmad(vb[2], vb[2], jmad(vb[1], vb[1], vb[0] * vb[0]));
-  const Jet qbar = 0.6125f * vb2;                                                       // base.py:240
-  const Jet invV = jrsqrt(vb2 + P.eps);                                                 // base.py:167
-  const Jet alpha = jatan2(vb[2], vb[0] + P.eps);                                       // base.py:176
-  const Jet beta = jasin(vb[1] * invV);                                                 // base.py:234
+  const J vb2 = jmad(vb[2], vb[2], jmad(vb[1], vb[1], vb[0] * vb[0]));
+  const J qbar = 0.6125f * vb2;                                                       // base.py:240
+  const J invV = jrsqrt(vb2 + P.eps);                                                 // base.py:167
+  const J alpha = jatan2(vb[2], vb[0] + P.eps);                                       // base.py:176
+  const J beta = jasin(vb[1] * invV);                                                 // base.py:234
 
-  Jet C[6];
+  J C[6];
   if constexpr (MODEL == 0) {
 #pragma unroll
-    for (int k = 0; k < 6; ++k) C[k] = jconst(P.net.c0[k]);
+    for (int k = 0; k < 6; ++k) C[k] = J::cst(P.net.c0[k]);
 #pragma unroll 2
     for (int j = 0; j < NH; ++j) {
       const HidPair& hp = P.net.hid[j >> 1];
       const int e = j & 1;
-      Jet h = jconst(hp.a0[e]);
+      J h = J::cst(hp.a0[e]);
       h = jfma(hp.Au[0][e], c.da, h);
       h = jfma(hp.Au[1][e], c.de, h);
       h = jfma(hp.Ax[0][e], qbar, h);
       h = jfma(hp.Ax[1][e], alpha, h);
       h = jfma(hp.Ax[2][e], beta, h);
-      const Jet r = jsigm2(h);
+      const J r = jsigm2(h);
 #pragma unroll
       for (int k = 0; k < 6; ++k) C[k] = jfma(P.net.Wo[k][j], r, C[k]);
     }
@@ -233,24 +235,24 @@ AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet 
   }
   C[5] = jfma(P.k_rudder, c.dr, C[5]);                       // coefficient_models.py:102-103
   if (P.stall_scaling) {                                     // aircraft.py:280-294
-    const Jet sa = jstall(alpha, 10.0f, 0.52359877559f), sbt = jstall(beta, 10.0f, 0.52359877559f);
+    const J sa = jstall(alpha, 10.0f, 0.52359877559f), sbt = jstall(beta, 10.0f, 0.52359877559f);
     C[2] = C[2] * sa * sbt;
     C[4] = C[4] * sa;
   }
   C[0] = jfma(P.k_flap_x, c.df, C[0]);                       // aircraft.py:297-299
   C[2] = jfma(P.k_flap_z, c.df, C[2]);
 
-  const Jet qS = P.S * qbar;
-  Jet F[3];
+  const J qS = P.S * qbar;
+  J F[3];
   F[0] = sign_casadi(vb[0].v) * (C[0] * qS);                 // sign() has zero derivative, as in CasADi
   F[1] = C[1] * qS;
   F[2] = C[2] * qS;
-  Jet Mo[3];
+  J Mo[3];
   Mo[0] = C[3] * (P.Sb * qbar) + (P.com[1] * F[2] - P.com[2] * F[1]);
   Mo[1] = C[4] * (P.Sc * qbar) + (P.com[2] * F[0] - P.com[0] * F[2]);
   Mo[2] = C[5] * (P.Sb * qbar) + (P.com[0] * F[1] - P.com[1] * F[0]);
 
-  const Jet sc = P.inv_mass * inv_n2;                        // base.py:284-286,359
+  const J sc = P.inv_mass * inv_n2;                        // base.py:284-286,359
 #pragma unroll
   for (int i = 0; i < 3; ++i)
     vdot[i] = jmad(M[3 * i + 2], F[2], jmad(M[3 * i + 1], F[1], M[3 * i] * F[0])) * sc + P.g[i];
@@ -260,7 +262,7 @@ AIRC_HD void f_jet(const DevConst& P, const Jet v[3], const Jet q[4], const Jet 
   qdot[2] = 0.5f * (s * w[2] + (x * w[1] - y * w[0]));
   qdot[3] = -0.5f * (x * w[0] + y * w[1] + z * w[2]);
   // w_dot = I^-1 (M - w x (I w))                            base.py:376-377
-  Jet Iw[3], t[3];
+  J Iw[3], t[3];
 #pragma unroll
   for (int i = 0; i < 3; ++i) Iw[i] = jfma(P.I[3 * i + 2], w[2], jfma(P.I[3 * i + 1], w[1], P.I[3 * i] * w[0]));
   t[0] = Mo[0] - (w[1] * Iw[2] - w[2] * Iw[1]);

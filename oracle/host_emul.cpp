@@ -12,6 +12,7 @@
 #include "../aircraft_b200/csrc/airc_coop.cuh"
 #include "../aircraft_b200/csrc/airc_sampler.cuh"
 #include "../aircraft_b200/csrc/airc_hess.cuh"
+#include "../aircraft_b200/csrc/airc_hess2.cuh"
 #include "../aircraft_b200/csrc/airc_jac.cuh"
 
 using namespace airc;
@@ -300,6 +301,41 @@ void emul_hessian(const AircParams* p, const AircNNBlob* nn, const float* x, con
       }
       if (seed.j0 == seed.i) g[zi] = L.o;
       if (t == 0) value[i] = L.v;
+    }
+  }
+}
+
+// K4 arithmetic (airc_hess2.cuh, forward over reverse): the eight lanes of a node, one after the other, and the
+// kernel's write-out (entries i <= j of column j with their mirror image).
+void emul_hessian2(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,
+                   float dt, int64_t n, int substeps, uint32_t flags, float* H, float* grad, float* value) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  alignas(16) float tab[NET_TAB_FLOATS];
+  for (int i = 0; i < NET_TAB_FLOATS; ++i) net_tab_entry(P, i, tab);
+  memset(H, 0, sizeof(float) * NZ * NZ * n);
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* Hn = H + i * NZ * NZ;
+    float* g = grad + i * NZ;
+    for (int r = 0; r < 3; ++r) { g[r] = lam[13 * i + r]; g[16 + r] = 0.f; }
+    for (int lane = 0; lane < HESS2_LANES; ++lane) {
+      Dual gd[NHACT];
+      float val;
+      hessian2_lane(P, tab, s, c, dt, substeps, (flags & AIRC_FLAG_NORMALISE) != 0, lam + 13 * i, lane, gd, val);
+      for (int half = 0; half < 2; ++half) {
+        const int j = 2 * lane + half;
+        if (j >= NHACT) continue;
+        for (int r = 0; r <= j; ++r) {
+          const float e = half ? gd[r].t.hi : gd[r].t.lo;
+          Hn[hess_zindex(r) * NZ + hess_zindex(j)] = Hn[hess_zindex(j) * NZ + hess_zindex(r)] = e;
+        }
+      }
+      if (lane == 0) {
+        for (int r = 0; r < NHACT; ++r) g[hess_zindex(r)] = gd[r].v;
+        value[i] = val;
+      }
     }
   }
 }

@@ -46,8 +46,8 @@ def test_hessian_parity(ac, orc, substeps, normalise, dt):
     assert np.abs(v.cpu().numpy() - vo).max() < PARITY_TOL * np.abs(vo).max()
 
 
-def test_hessian_structure_layouts_and_host_path(ac):
-    n = 300
+@pytest.mark.parametrize("n", [300, 1500])            # the jets kernel / the forward-over-reverse kernel
+def test_hessian_structure_layouts_and_host_path(ac, n):
     x, u, lam = _inputs(n, 52)
     H, g, _ = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.01)
     assert torch.equal(H, H.transpose(1, 2))
@@ -59,14 +59,41 @@ def test_hessian_structure_layouts_and_host_path(ac):
     Hh, gh, _ = ac.lagrangian_hessian(x, u, lam, 0.01)
     assert isinstance(Hh, np.ndarray) and np.array_equal(Hh, H.cpu().numpy()) and np.array_equal(gh, g.cpu().numpy())
     # leading batch dims are kept: [windows, nodes, ...]
-    Hw, gw, _ = ac.lagrangian_hessian(f32(x.reshape(6, 50, 13)), f32(u.reshape(6, 50, 7)),
-                                      f32(lam.reshape(6, 50, 13)), 0.01)
-    assert Hw.shape == (6, 50, 21, 21) and torch.equal(Hw.reshape(n, 21, 21), H)
+    Hw, gw, _ = ac.lagrangian_hessian(f32(x.reshape(6, n // 6, 13)), f32(u.reshape(6, n // 6, 7)),
+                                      f32(lam.reshape(6, n // 6, 13)), 0.01)
+    assert Hw.shape == (6, n // 6, 21, 21) and torch.equal(Hw.reshape(n, 21, 21), H)
     # linear in the multipliers
     H2, g2, _ = ac.lagrangian_hessian(f32(x), f32(u), f32(2 * lam), 0.01)
     assert col_err(H2.cpu(), 2 * H.cpu().numpy()) < 1e-6
     with pytest.raises(RuntimeError):
         ac.lagrangian_hessian(f32(x), f32(u), f32(lam[:, :12]), 0.01)
+
+
+def test_hessian_two_formulations_agree(ac, orc):
+    """airc_hessian runs the network model's long batches by forward over reverse (airc_hess2.cuh, eight lanes per
+    node sharing the network through shuffles) and short horizons (up to three nodes per SM) on second-order
+    jets (airc_hess.cuh): the same nodes through both, against each other and against the oracle, and the last
+    partial warp of the long batch (idle lanes keep step for the shuffles)."""
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    n_short, n_long = 3 * sms, 3 * sms + 5           # 5 nodes = 40 lanes: one full warp and a quarter of the next
+    x, u, lam = _inputs(n_long, 54)
+    Hl, gl, vl = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.02, normalise=True, want_value=True)
+    Hs, gs, vs = ac.lagrangian_hessian(f32(x[:n_short]), f32(u[:n_short]), f32(lam[:n_short]), 0.02, normalise=True,
+                                       want_value=True)
+    assert not torch.equal(Hl[:n_short], Hs)          # two different arithmetics ...
+    assert col_err(Hl[:n_short].cpu(), Hs.cpu().numpy()) < 2e-6 and col_err(gl[:n_short].cpu(), gs.cpu().numpy()) < 2e-6
+    Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.02, 1, True))
+    assert col_err(Hl.cpu(), Ho) < PARITY_TOL and col_err(gl.cpu(), go) < PARITY_TOL
+    assert col_err(Hs.cpu(), Ho[:n_short]) < PARITY_TOL
+    assert np.abs(vl.cpu().numpy() - vo).max() < PARITY_TOL * np.abs(vo).max()
+    assert torch.equal(Hl, Hl.transpose(1, 2))
+    # more substeps than the reverse sweep keeps start states for: the jets again, same answer as the oracle
+    H9, g9, _ = ac.lagrangian_hessian(f32(x[:600]), f32(u[:600]), f32(lam[:600]), 0.02, substeps=9)
+    Ho9, go9, _ = (a.numpy() for a in orc.lagrangian_hessian(t64(x[:600]), t64(u[:600]), t64(lam[:600]), 0.02, 9, False))
+    assert col_err(H9.cpu(), Ho9) < PARITY_TOL and col_err(g9.cpu(), go9) < PARITY_TOL
+    H8, g8, _ = ac.lagrangian_hessian(f32(x[:600]), f32(u[:600]), f32(lam[:600]), 0.02, substeps=8, normalise=True)
+    Ho8, go8, _ = (a.numpy() for a in orc.lagrangian_hessian(t64(x[:600]), t64(u[:600]), t64(lam[:600]), 0.02, 8, True))
+    assert col_err(H8.cpu(), Ho8) < PARITY_TOL and col_err(g8.cpu(), go8) < PARITY_TOL
 
 
 def test_hessian_gradient_matches_jacobian_kernel(ac):

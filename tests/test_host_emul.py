@@ -92,15 +92,18 @@ def test_linearize_packed_dt_column(pair, substeps, normalise):
     assert np.allclose(D0.numpy(), orc.state_derivative(t64(x), t64(u)).numpy(), rtol=1e-6, atol=1e-6)
 
 
-@pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (2, True)])
-def test_lagrangian_hessian_jets(pair, substeps, normalise):
-    """K3 arithmetic (airc_jet.cuh / airc_hess.cuh: second-order forward mode, 64 (outer, inner-pair)
-    tasks per node) against jacfwd(jacfwd(lam^T Phi)) of the float64 oracle over z = (x, u, dt)."""
+@pytest.mark.parametrize("arith", ["hessian2", "hessian"])
+@pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (2, True), (3, False)])
+def test_lagrangian_hessian_jets(pair, substeps, normalise, arith):
+    """K4 arithmetic against jacfwd(jacfwd(lam^T Phi)) of the float64 oracle over z = (x, u, dt), both forms:
+    `hessian2` = forward over reverse (airc_hess2.cuh: the hand-written adjoint sweep of the RK4 step on dual
+    numbers, eight lanes per node; what airc_hessian runs for the network model), `hessian` = second-order
+    forward mode (airc_jet.cuh / airc_hess.cuh: 64 (outer, inner-pair) tasks per node; the table models)."""
     emu, orc = pair
     n = 96
     x, u = make_states(n, seed=27, perturb_norm=1e-3), make_controls(n, seed=27)
     lam = np.random.default_rng(27).normal(size=(n, 13)).astype(np.float32)
-    H, g, v = emu.hessian(x, u, lam, 0.02, substeps, normalise)
+    H, g, v = getattr(emu, arith)(x, u, lam, 0.02, substeps, normalise)
     Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.02, substeps, normalise))
     assert col_err(H, Ho, atol=1e-3) < PARITY_TOL        # every entry against its own scale over the batch
     assert col_err(g, go) < PARITY_TOL
@@ -121,9 +124,11 @@ def test_lagrangian_hessian_jets_stall_scaling(built):
     x, u = make_states(n, seed=28), make_controls(n, seed=28)
     x[:32, 3:6] *= np.array([0.6, 1.0, 2.0])             # large alpha: the scaling is active
     lam = np.random.default_rng(28).normal(size=(n, 13)).astype(np.float32)
-    H, g, v = emu.hessian(x, u, lam, 0.01)
     Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.01))
-    assert col_err(H, Ho, atol=1e-3) < PARITY_TOL and col_err(g, go) < PARITY_TOL
+    for arith in (emu.hessian2, emu.hessian):
+        H, g, v = arith(x, u, lam, 0.01)
+        assert col_err(H, Ho, atol=1e-3) < PARITY_TOL and col_err(g, go) < PARITY_TOL
+        assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
 
 
 @pytest.mark.parametrize("normalise", [False, True])
