@@ -399,9 +399,15 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   if (!h->dc.model && substeps <= HESS2_MAXSUB && !AIRC_AB_HESS_JETS && n > (long long)AIRC_AB_HESS_SMALL * h->sm_count) {
     // the NN surrogate: forward over reverse, eight threads per node (airc_hess2.cuh).  Short horizons (up to
     // three nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
-    const unsigned grid = (unsigned)((n * HESS2_LANES + bs - 1) / bs);
-    if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true><<<grid, bs, 0, st>>>(h->dc, a);
-    else hessian2_kernel<false><<<grid, bs, 0, st>>>(h->dc, a);
+    const int bs2 = AIRC_AB_H2_BS ? AIRC_AB_H2_BS : (n * HESS2_LANES >= (long long)h->sm_count * 256 * 8 ? 256 : 128);
+    const unsigned grid = (unsigned)((n * HESS2_LANES + bs2 - 1) / bs2);
+    if (bs2 == 256) {
+      if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true, 256><<<grid, 256, 0, st>>>(h->dc, a);
+      else hessian2_kernel<false, 256><<<grid, 256, 0, st>>>(h->dc, a);
+    } else {
+      if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true, 128><<<grid, 128, 0, st>>>(h->dc, a);
+      else hessian2_kernel<false, 128><<<grid, 128, 0, st>>>(h->dc, a);
+    }
     return check_launch();
   }
   // table models, short horizons, and more substeps than the reverse sweep keeps: second-order jets, 64 threads per node

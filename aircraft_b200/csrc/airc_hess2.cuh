@@ -19,8 +19,8 @@
 #ifndef AIRC_AB_H2_MINB            // build-variant A/B only
 #define AIRC_AB_H2_MINB 1
 #endif
-#ifndef AIRC_AB_H2_UNROLL
-#define AIRC_AB_H2_UNROLL 2
+#ifndef AIRC_AB_H2_BS              // 0: 256 threads per block for long batches, 128 below (shipped); else fixed
+#define AIRC_AB_H2_BS 0
 #endif
 
 namespace airc {
@@ -577,11 +577,14 @@ AIRC_HD void hessian2_lane(const DevConst& P, const float* tab, const State& x0,
 }
 
 #if defined(__CUDACC__)
-template <bool SOA>
-__global__ void __launch_bounds__(128, AIRC_AB_H2_MINB)
+// BS: 256 (one block per SM at 255 registers) keeps the eight warps of an SM close together in the long
+// straight-line code, whose fetch is the limiter otherwise (+17 % over two blocks of 128); 128 spreads shorter
+// batches over more SMs and wastes less in the last wave.
+template <bool SOA, int BS>
+__global__ void __launch_bounds__(BS, AIRC_AB_H2_MINB)
 hessian2_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
   __shared__ __align__(16) float tab[NET_TAB_FLOATS];
-  for (int i = threadIdx.x; i < NET_TAB_FLOATS; i += blockDim.x) net_tab_entry(P, i, tab);
+  for (int i = threadIdx.x; i < NET_TAB_FLOATS; i += BS) net_tab_entry(P, i, tab);
   __syncthreads();
   const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = gt / HESS2_LANES < a.n;
