@@ -578,7 +578,9 @@ class Aircraft:
 
         layout 'aos': x[...,13], u[...,7], lam[...,13] -> H[...,21,21], grad[...,21], value[...]
         layout 'soa': x[13,N],  u[7,N],  lam[13,N]   -> H[21,21,N],   grad[21,N],   value[N]
-        Returns (H, grad, value) with None for the parts not requested."""
+        Returns (H, grad, value) with None for the parts not requested.  Long batches of the network model are
+        differentiated forward over reverse, short horizons and the table models by second-order forward mode
+        (include/aircraft_b200.h, airc_hessian); both are exact derivatives, equal to 5e-7 of an entry's scale."""
         if layout not in ("aos", "soa"):
             raise RuntimeError(f"layout must be 'aos' or 'soa', got {layout!r}")
         soa = layout == "soa"

@@ -14,6 +14,7 @@
 // pass rebuilds each stage point from them and f_vjp recomputes f's interior.  Only the NN surrogate
 // (model 0) has a hand-written adjoint; the table models stay on airc_hess.cuh.
 #pragma once
+#include <type_traits>
 #include "airc_hess.cuh"
 
 #ifndef AIRC_AB_H2_MINB            // build-variant A/B only
@@ -23,13 +24,43 @@
 #define AIRC_AB_H2_BS 0
 #endif
 
+#ifndef AIRC_AB_H2_DIRS            // directions per lane: 2 (eight lanes per node, shipped) or 4 (four lanes)
+#define AIRC_AB_H2_DIRS 2
+#endif
+
 namespace airc {
 
-// value + derivatives along two directions
+constexpr int H2_DIRS = AIRC_AB_H2_DIRS;
+constexpr int HESS2_LANES = (15 + H2_DIRS - 1) / H2_DIRS;   // threads per node
+static_assert(H2_DIRS == 2 || H2_DIRS == 4, "two or four directions per lane");
+
+// two packed pairs, for the four-direction variant
+struct F4 {
+  F2 a, b;
+};
+AIRC_HD F4 add2(const F4& x, const F4& y) { return F4{add2(x.a, y.a), add2(x.b, y.b)}; }
+AIRC_HD F4 tsub(const F4& x, const F4& y) { return F4{tsub(x.a, y.a), tsub(x.b, y.b)}; }
+AIRC_HD F4 neg2(const F4& x) { return F4{neg2(x.a), neg2(x.b)}; }
+AIRC_HD F4 tmul(float s, const F4& x) { return F4{tmul(s, x.a), tmul(s, x.b)}; }
+AIRC_HD F4 tfma(float s, const F4& x, const F4& y) { return F4{tfma(s, x.a, y.a), tfma(s, x.b, y.b)}; }
+template <class T> struct TanOps;
+template <> struct TanOps<F2> {
+  static AIRC_HD F2 zero() { return F2{0.0f, 0.0f}; }
+  static AIRC_HD F2 unit(int slot, int first) { return F2{slot == first ? 1.0f : 0.0f, slot == first + 1 ? 1.0f : 0.0f}; }
+  static AIRC_HD float get(const F2& t, int i) { return i ? t.hi : t.lo; }
+};
+template <> struct TanOps<F4> {
+  static AIRC_HD F4 zero() { return F4{F2{0.0f, 0.0f}, F2{0.0f, 0.0f}}; }
+  static AIRC_HD F4 unit(int slot, int first) { return F4{TanOps<F2>::unit(slot, first), TanOps<F2>::unit(slot, first + 2)}; }
+  static AIRC_HD float get(const F4& t, int i) { return i < 2 ? TanOps<F2>::get(t.a, i) : TanOps<F2>::get(t.b, i - 2); }
+};
+using Tan = std::conditional<H2_DIRS == 2, F2, F4>::type;
+
+// value + derivatives along H2_DIRS directions
 struct Dual {
   float v;
-  F2 t;
-  static AIRC_HD Dual cst(float c) { return Dual{c, F2{0.0f, 0.0f}}; }
+  Tan t;
+  static AIRC_HD Dual cst(float c) { return Dual{c, TanOps<Tan>::zero()}; }
 };
 
 AIRC_HD Dual operator+(const Dual& a, const Dual& b) { return Dual{a.v + b.v, add2(a.t, b.t)}; }
@@ -101,13 +132,14 @@ AIRC_HD void dcross(const Dual a[3], const Dual b[3], Dual o[3]) {
 //   C = c0 + Wo r(h),   J = dC/dy = Wo diag(r') A   (6 x 5),   G = sum_j (Wo^T Cb)_j r''_j a_j a_j^T   (5 x 5, symmetric)
 // for the inputs y = (aileron, elevator, qbar, alpha, beta), h = a0 + A y.  With them the dual parts are small
 // products:  C.t = J y.t,   yb = J^T Cb,   yb.t = J^T Cb.t + G y.t   (G is the second derivative of Cb^T C).
-constexpr int NET_TAB_FLOATS = 4 * 8 * 12;   // [unit of the lane][lane][a0, a(5), Wo(6)]
+constexpr int NET_UNITS = NH / HESS2_LANES;  // hidden units per lane
+constexpr int NET_TAB_FLOATS = NH * 12;      // [unit of the lane][lane][a0, a(5), Wo(6)]
 constexpr int NET_NC = 6, NET_NJ = 30, NET_NG = 15;
 
 // the weight image a lane reads its units from (shared memory on the device: conflict-free LDS.128)
 AIRC_HD void net_tab_entry(const DevConst& P, int idx, float* tab) {   // idx in [0, 32*12)
-  const int f = idx % 12, sub = (idx / 12) % 8, loc = idx / 96;
-  const int j = 4 * sub + loc;
+  const int f = idx % 12, sub = (idx / 12) % HESS2_LANES, loc = idx / (12 * HESS2_LANES);
+  const int j = NET_UNITS * sub + loc;
   const HidPair& hp = P.net.hid[j >> 1];
   const int e = j & 1;
   float v;
@@ -125,9 +157,9 @@ AIRC_HD void net_share(const float* tab, int sub, const float y[5], const float 
 #pragma unroll
   for (int i = 0; i < NACC; ++i) acc[i] = 0.0f;
 #pragma unroll
-  for (int loc = 0; loc < 4; ++loc) {
+  for (int loc = 0; loc < NET_UNITS; ++loc) {
     struct alignas(16) Q4 { float x, y, z, w; };   // three 16-byte loads
-    const Q4* wp = reinterpret_cast<const Q4*>(tab + (loc * 8 + sub) * 12);
+    const Q4* wp = reinterpret_cast<const Q4*>(tab + (loc * HESS2_LANES + sub) * 12);
     const Q4 w0 = wp[0], w1 = wp[1], w2 = wp[2];
     const float a[5] = {w0.y, w0.z, w0.w, w1.x, w1.y};
     const float wo[6] = {w1.z, w1.w, w2.x, w2.y, w2.z, w2.w};
@@ -171,15 +203,18 @@ AIRC_HD void net_linearise(const DevConst& P, const float* tab, int sub, const f
 #if defined(__CUDA_ARCH__)
   net_share<ADJ>(tab, sub, y, Cbv, acc);
 #pragma unroll
-  for (int d = 1; d < 8; d <<= 1)
+  for (int d = 1; d < HESS2_LANES; d <<= 1)
 #pragma unroll
     for (int i = 0; i < NACC; ++i) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], d);
 #else
   (void)sub;
-  float part[8][NACC];
-  for (int l = 0; l < 8; ++l) net_share<ADJ>(tab, l, y, Cbv, part[l]);
-  for (int i = 0; i < NACC; ++i)
-    acc[i] = ((part[0][i] + part[1][i]) + (part[2][i] + part[3][i])) + ((part[4][i] + part[5][i]) + (part[6][i] + part[7][i]));
+  float part[HESS2_LANES][NACC];
+  for (int l = 0; l < HESS2_LANES; ++l) net_share<ADJ>(tab, l, y, Cbv, part[l]);
+  for (int d = 1; d < HESS2_LANES; d <<= 1)      // the butterfly: after level d, part[l] holds the sum of its group of 2d
+    for (int l = 0; l < HESS2_LANES; ++l)
+      if (!(l & d))
+        for (int i = 0; i < NACC; ++i) part[l][i] = part[l | d][i] = part[l][i] + part[l | d][i];
+  for (int i = 0; i < NACC; ++i) acc[i] = part[0][i];
 #endif
 #pragma unroll
   for (int k = 0; k < 6; ++k) acc[k] += P.net.c0[k];
@@ -294,7 +329,7 @@ AIRC_HD void f_dual(const DevConst& P, const float* tab, int sub, const DState& 
     const float* J = acc + NET_NC;
 #pragma unroll
     for (int kk = 0; kk < 6; ++kk) {
-      F2 t = tmul(J[5 * kk], yin[0]->t);
+      Tan t = tmul(J[5 * kk], yin[0]->t);
 #pragma unroll
       for (int i = 1; i < 5; ++i) t = tfma(J[5 * kk + i], yin[i]->t, t);
       C[kk] = Dual{acc[kk], t};
@@ -416,7 +451,6 @@ AIRC_HD void f_dual(const DevConst& P, const float* tab, int sub, const DState& 
   }
 }
 
-constexpr int HESS2_LANES = 8;     // threads per node, two of the 15 active directions each
 constexpr int HESS2_MAXSUB = 8;    // substeps whose start states the reverse sweep keeps; beyond: airc_hess.cuh
 
 // One RK4 substep forward on duals (base.py:408-480): k1..k3 into ks, and with `advance` also k4 and x <- x+.
@@ -508,8 +542,8 @@ AIRC_HD void rk4_reverse_dual(const DevConst& P, const float* tab, int sub, cons
 // sums cross them); the host runs them one after the other.
 AIRC_HD void hessian2_lane(const DevConst& P, const float* tab, const State& x0, const Ctl& c0, float dt, int substeps,
                            bool normalise, const float lam[13], int lane, Dual g[NHACT], float& value) {
-  const int j0 = 2 * lane, j1 = j0 + 1;
-  auto seed = [&](float val, int slot) { return Dual{val, F2{slot == j0 ? 1.0f : 0.0f, slot == j1 ? 1.0f : 0.0f}}; };
+  const int j0 = H2_DIRS * lane;
+  auto seed = [&](float val, int slot) { return Dual{val, TanOps<Tan>::unit(slot, j0)}; };
   DState x;
 #pragma unroll
   for (int i = 0; i < 3; ++i) { x.e[i] = seed(x0.v[i], i); x.e[7 + i] = seed(x0.w[i], 7 + i); }
@@ -606,15 +640,15 @@ hessian2_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
   // column j of the active block comes from one lane: entries (i <= j) are written with their mirror image,
   // so H is symmetric to the bit
 #pragma unroll
-  for (int half = 0; half < 2; ++half) {
-    const int j = 2 * lane + half;
+  for (int half = 0; half < H2_DIRS; ++half) {
+    const int j = H2_DIRS * lane + half;
     if (j < NHACT) {
       const int zj = hess_zindex(j);
 #pragma unroll
       for (int i = 0; i < NHACT; ++i)
         if (i <= j) {
           const int zi = hess_zindex(i);
-          const float val = half ? g[i].t.hi : g[i].t.lo;
+          const float val = TanOps<Tan>::get(g[i].t, half);
           Hn[(zi * NZ + zj) * es] = val;
           Hn[(zj * NZ + zi) * es] = val;
         }

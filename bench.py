@@ -835,22 +835,28 @@ def side_extras(torch, ac, dev, args):
         lam = torch.randn(13, nh, device=dev, generator=torch.Generator(device=dev).manual_seed(600 + rank))
         ms = time_launches(torch, lambda: ac.lagrangian_hessian(x, u, lam, DT, layout="soa", normalise=True), K, 3, flush)
         out[name] = {"workload": f"d2(lambda^T Phi)/d(x,u,dt)^2 [21x21] + gradient at {nh} shooting nodes (SoA)",
+                     "kernel": "second-order jets, 64 threads per node (short horizon)"
+                               if nh <= 3 * torch.cuda.get_device_properties(dev).multi_processor_count
+                               else "forward over reverse, 8 lanes per node",
                      "value": nh / (ms * 1e-3), "unit": "hessian-evals/s", "ms_per_launch": ms,
                      "l2": "flushed between launches",
                      "reference_context": "nlp_hess_l 56-560 ms per IPOPT iteration at 298 nodes (reference todo.md tables, CPU)"}
-        aud = kernel_audit("hessian")
+        aud = kernel_audit("hessian2")
         if aud and name == "hessian_bulk":
             ex, by = aud["executed_fp32_flops_per_unit"], aud["dram_bytes_per_unit"]
             tf = nh * ex / (ms * 1e-3) / 1e12
             pk = fp32_peak(ac)
             out[name]["roofline"] = {
-                "kernel": "hessian_kernel<soa> (second-order forward mode on jets, 64 threads per node)", "bound": "fp32",
+                "kernel": "hessian2_kernel<soa, 256> (forward over reverse on dual numbers, 8 lanes per node)", "bound": "fp32",
                 "achieved": tf, "peak": pk, "unit": "TFLOP/s", "frac": tf / pk,
                 "executed_flops_per_eval": ex, "dram_bytes_per_eval": by,
                 "algorithmic_bytes_per_eval": 4 * (13 + 7 + 13 + 441 + 21),
-                "source": f"profiles/{aud['capture']} via profiles/r2_kernel_audit.json (EXECUTED flops: this kernel re-evaluates "
-                          f"the value and outer-direction parts in every thread, so executed work overstates the useful "
-                          f"work ~3x); CUDA sources {'CHANGED since' if aud['stale'] else 'unchanged since'} the capture"}
+                "issue_active_pct_under_ncu": aud.get("issue_active_pct"),
+                "note": "instruction-fetch bound rather than FMA bound: ~17 k straight-line instructions per thread with "
+                        "two warps per scheduler (profiles/r2_variants_hessian.txt); the value parts are the same in the "
+                        "eight lanes of a node, so about a third of the executed flops are replicated work",
+                "source": f"profiles/{aud['capture']} via profiles/r2_kernel_audit.json (EXECUTED flops); CUDA sources "
+                          f"{'CHANGED since' if aud['stale'] else 'unchanged since'} the capture"}
     return out
 
 

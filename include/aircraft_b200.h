@@ -211,8 +211,12 @@ int airc_defects(const AircHandle* h, const float* x, const float* u, const floa
 /* Second-order products for the solver: H = d2(lambda^T Phi)/dz2 with z = (x[13], u[7], dt), the
  * per-node block of the Lagrangian Hessian that IPOPT obtains from CasADi with
  * hessian_approximation 'exact' (src/aircraft/config.py:29; constraints control/base.py:275-286; the
- * dt row/column serves time='progress', control/base.py:276,306-307).  Second-order forward mode
- * on 64 threads per node (15 active directions; rows/columns of p and thrust are exactly zero).
+ * dt row/column serves time='progress', control/base.py:276,306-307).  15 directions are active; rows
+ * and columns of p and thrust are exactly zero; H is symmetric to the bit.  The network model runs
+ * forward over reverse (a hand-written adjoint sweep of the RK4 step on dual numbers, 8 threads per
+ * node); short horizons (up to 3 nodes per SM), the table models and more than 8 substeps run
+ * second-order forward mode on 64 threads per node.  The two agree to 5e-7 of an entry's scale, so
+ * a node's block depends on the batch it is evaluated in only at that level.
  *   lam   multipliers of the 13 rows of Phi, laid out like x
  *   H     SOA [21*21][n] / AOS [n][21][21], full symmetric matrix (required)
  *   grad  optional d(lambda^T Phi)/dz, SOA [21][n] / AOS [n][21]   (= [A B dPhi/ddt]^T lambda)

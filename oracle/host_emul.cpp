@@ -324,11 +324,11 @@ void emul_hessian2(const AircParams* p, const AircNNBlob* nn, const float* x, co
       Dual gd[NHACT];
       float val;
       hessian2_lane(P, tab, s, c, dt, substeps, (flags & AIRC_FLAG_NORMALISE) != 0, lam + 13 * i, lane, gd, val);
-      for (int half = 0; half < 2; ++half) {
-        const int j = 2 * lane + half;
+      for (int half = 0; half < H2_DIRS; ++half) {
+        const int j = H2_DIRS * lane + half;
         if (j >= NHACT) continue;
         for (int r = 0; r <= j; ++r) {
-          const float e = half ? gd[r].t.hi : gd[r].t.lo;
+          const float e = TanOps<Tan>::get(gd[r].t, half);
           Hn[hess_zindex(r) * NZ + hess_zindex(j)] = Hn[hess_zindex(j) * NZ + hess_zindex(r)] = e;
         }
       }
