@@ -401,13 +401,17 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
     // three nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
     const int bs2 = AIRC_AB_H2_BS ? AIRC_AB_H2_BS : (n * HESS2_LANES >= (long long)h->sm_count * 256 * 8 ? 256 : 128);
     const unsigned grid = (unsigned)((n * HESS2_LANES + bs2 - 1) / bs2);
-    if (bs2 == 256) {
-      if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true, 256><<<grid, 256, 0, st>>>(h->dc, a);
-      else hessian2_kernel<false, 256><<<grid, 256, 0, st>>>(h->dc, a);
-    } else {
-      if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true, 128><<<grid, 128, 0, st>>>(h->dc, a);
-      else hessian2_kernel<false, 128><<<grid, 128, 0, st>>>(h->dc, a);
-    }
+#define AIRC_H2_LAUNCH(BS_)                                                                   \
+    do {                                                                                      \
+      if (layout == AIRC_LAYOUT_SOA) hessian2_kernel<true, BS_><<<grid, BS_, 0, st>>>(h->dc, a); \
+      else hessian2_kernel<false, BS_><<<grid, BS_, 0, st>>>(h->dc, a);                       \
+    } while (0)
+    if (bs2 == 256) AIRC_H2_LAUNCH(256);
+#if AIRC_AB_H2_BS && AIRC_AB_H2_BS != 128 && AIRC_AB_H2_BS != 256
+    else if (bs2 == AIRC_AB_H2_BS) AIRC_H2_LAUNCH(AIRC_AB_H2_BS);
+#endif
+    else AIRC_H2_LAUNCH(128);
+#undef AIRC_H2_LAUNCH
     return check_launch();
   }
   // table models, short horizons, and more substeps than the reverse sweep keeps: second-order jets, 64 threads per node
