@@ -414,7 +414,16 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
 #undef AIRC_H2_LAUNCH
     return check_launch();
   }
-  // table models, short horizons, and more substeps than the reverse sweep keeps: second-order jets, 64 threads per node
+#ifndef AIRC_AB_HESS_SHARED        // build-variant A/B only: 0 keeps short horizons on the unshared jets kernel
+#define AIRC_AB_HESS_SHARED 1
+#endif
+  if (!h->dc.model && AIRC_AB_HESS_SHARED && n <= (long long)AIRC_AB_HESS_SMALL * h->sm_count) {
+    // short horizons of the network model: jets, one node per 64-thread block, the network shared by the block
+    if (layout == AIRC_LAYOUT_SOA) hessian_kernel<true, 0, true><<<(unsigned)n, HESS_LANES, 0, st>>>(h->dc, a);
+    else hessian_kernel<false, 0, true><<<(unsigned)n, HESS_LANES, 0, st>>>(h->dc, a);
+    return check_launch();
+  }
+  // table models, and more substeps than the reverse sweep keeps: second-order jets, 64 threads per node
   const long long threads = n * HESS_LANES;
   const unsigned grid = (unsigned)((threads + bs - 1) / bs);
   if (h->dc.model) {

@@ -73,10 +73,137 @@ struct PRows {
   }
 };
 
+// ---- the network shared by the 64 threads of a node (short horizons) --------------------------------------
+// The value-level sums over the 32 hidden units are the same in all 64 threads of a node (they differ in their
+// directions only): C = c0 + Wo r, J = dC/dy (6 x 5) and T_k = d2 C_k / dy2 (six symmetric 5 x 5: 90 numbers),
+// y = (aileron, elevator, qbar, alpha, beta).  Thread t takes hidden unit t mod 32 and one half of the 126 terms,
+// the terms go through shared memory, thread t adds columns t and t + 64 over the 32 units, and every thread
+// reads the 126 sums back.  A jet of C_k is then
+//   v = C_k,  o = J_k y.o,  g = J_k y.g,  og = J_k y.og + (y.o^T T_k) y.g.
+// This shortens the dependency chain of one f evaluation from ~3 000 to ~1 900 instructions, which is what a
+// short horizon (one warp per scheduler) waits for.
+constexpr int NJS_SUMS = 6 + 30 + 90, NJS_ROW = NJS_SUMS + 1, NJS_HALF = 6 + 30 + 30;
+
+// the terms [0, NJS_HALF) (HALF 0) or [NJS_HALF, NJS_SUMS) (HALF 1) of one hidden unit; w = (a0, a[5], Wo[6])
+template <int HALF>
+AIRC_HD void net_unit_terms(const float w[12], const float y[5], float* out) {
+  float h = w[0];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) h = fmaf(w[1 + i], y[i], h);
+  const float r = sigm2(h);
+  const float r1 = -0.69314718056f * r * (1.0f - r);
+  const float r2 = -0.69314718056f * (1.0f - 2.0f * r) * r1;
+  float qq[15];
+  {
+    int e = 0;
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+      const float t = r2 * w[1 + i];
+#pragma unroll
+      for (int l = i; l < 5; ++l, ++e) qq[e] = t * w[1 + l];
+    }
+  }
+  if (HALF == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      out[k] = w[6 + k] * r;
+      const float wr = w[6 + k] * r1;
+#pragma unroll
+      for (int i = 0; i < 5; ++i) out[6 + 5 * k + i] = wr * w[1 + i];
+    }
+  }
+#pragma unroll
+  for (int k = (HALF ? 2 : 0); k < (HALF ? 6 : 2); ++k)
+#pragma unroll
+    for (int e = 0; e < 15; ++e) out[36 + 15 * k + e] = w[6 + k] * qq[e];
+}
+
+AIRC_HD void net_unit_weights(const DevConst& P, int j, float w[12]) {
+  const HidPair& hp = P.net.hid[j >> 1];
+  const int e = j & 1;
+  w[0] = hp.a0[e];
+  w[1] = hp.Au[0][e]; w[2] = hp.Au[1][e];
+  w[3] = hp.Ax[0][e]; w[4] = hp.Ax[1][e]; w[5] = hp.Ax[2][e];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) w[6 + k] = P.net.Wo[k][j];
+}
+
+struct NetSharedJet {
+  float* prod;    // device: [32][NJS_ROW] in shared memory; host: unused
+  float* sums;    // device: [NJS_SUMS] in shared memory; host: unused
+  int t;          // thread of the node, 0..63
+  float w[12];    // device: the weights of hidden unit t mod 32
+
+  AIRC_HD void operator()(const DevConst& P, const Jet& da, const Jet& de, const Jet& qbar, const Jet& alpha,
+                          const Jet& beta, Jet C[6]) const {
+    const Jet* yin[5] = {&da, &de, &qbar, &alpha, &beta};
+    const float y[5] = {da.v, de.v, qbar.v, alpha.v, beta.v};
+    float S[NJS_SUMS];
+#if defined(__CUDA_ARCH__)
+    {
+      float* row = prod + (t & 31) * NJS_ROW;
+      if (t < 32) net_unit_terms<0>(w, y, row);
+      else net_unit_terms<1>(w, y, row);
+      __syncthreads();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const int m = t + 64 * c;
+        if (m < NJS_SUMS) {
+          float a = prod[m];
+#pragma unroll 8
+          for (int j = 1; j < 32; ++j) a += prod[j * NJS_ROW + m];
+          sums[m] = a;
+        }
+      }
+      __syncthreads();
+#pragma unroll
+      for (int m = 0; m < NJS_SUMS; ++m) S[m] = sums[m];
+    }
+#else
+    {   // the same terms, added in the same order (units 0..31)
+      float term[NJS_SUMS], ww[12];
+      for (int j = 0; j < 32; ++j) {
+        net_unit_weights(P, j, ww);
+        net_unit_terms<0>(ww, y, term);
+        net_unit_terms<1>(ww, y, term);
+        for (int m = 0; m < NJS_SUMS; ++m) S[m] = j ? S[m] + term[m] : term[m];
+      }
+    }
+#endif
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+      const float* Jk = S + 6 + 5 * k;
+      const float* Tk = S + 36 + 15 * k;
+      Jet r;
+      r.v = P.net.c0[k] + S[k];
+      r.o = Jk[0] * yin[0]->o;
+      r.g = tmul(Jk[0], yin[0]->g);
+      r.og = tmul(Jk[0], yin[0]->og);
+#pragma unroll
+      for (int i = 1; i < 5; ++i) {
+        r.o = fmaf(Jk[i], yin[i]->o, r.o);
+        r.g = tfma(Jk[i], yin[i]->g, r.g);
+        r.og = tfma(Jk[i], yin[i]->og, r.og);
+      }
+#pragma unroll
+      for (int l = 0; l < 5; ++l) {   // u_l = sum_i T_k[i][l] y_i.o
+        float u = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+          const int lo = i < l ? i : l, hi = i < l ? l : i;
+          u = fmaf(Tk[lo * 5 - (lo * (lo - 1)) / 2 + (hi - lo)], yin[i]->o, u);
+        }
+        r.og = tfma(u, yin[l]->g, r.og);
+      }
+      C[k] = r;
+    }
+  }
+};
+
 // Phi(x,u,dt) on jets (base.py:408-480): v, q, w in place; the p rows through PA.
-template <int MODEL, class PA>
+template <int MODEL, class PA, class NET = NetInlineJet>
 AIRC_HD void state_update_jet(const DevConst& P, Jet v[3], Jet q[4], Jet w[3], const CtlJ& c, const Jet& h,
-                              int substeps, bool normalise, PA& pa) {
+                              int substeps, bool normalise, PA& pa, const NET& net = NET()) {
   const Jet hh = 0.5f * h, h6 = (1.0f / 6.0f) * h;
   for (int sub = 0; sub < substeps; ++sub) {
     Jet sv[3], sq[4], sw[3], av[3], aq[4], aw[3];
@@ -89,7 +216,7 @@ AIRC_HD void state_update_jet(const DevConst& P, Jet v[3], Jet q[4], Jet w[3], c
     for (int stage = 0; stage < 4; ++stage) {
       const float wgt = (stage == 0 || stage == 3) ? 1.0f : 2.0f;
       Jet kv[3], kq[4], kw[3];
-      f_jet<MODEL>(P, sv, sq, sw, c, kv, kq, kw);
+      f_jet<MODEL, Jet, NET>(P, sv, sq, sw, c, kv, kq, kw, net);
       pa.stage(wgt, sv);
       const Jet cn = (stage == 2) ? h : hh;
 #pragma unroll
@@ -129,16 +256,16 @@ AIRC_HD void seed_state_jet(const State& x0, const Ctl& c0, float dt, int subste
 }
 
 // lambda^T Phi(x,u,dt) on jets.  lam[13] in state order.  Returns the jet of the scalar.
-template <int MODEL = 0>
+template <int MODEL = 0, class NET = NetInlineJet>
 AIRC_HD Jet lagrangian_step_jet(const DevConst& P, const State& x0, const Ctl& c0, float dt, int substeps,
-                                bool normalise, const float lam[13], const HessSeed& seed) {
+                                bool normalise, const float lam[13], const HessSeed& seed, const NET& net = NET()) {
   Jet v[3], q[4], w[3], h;
   CtlJ c;
   seed_state_jet(x0, c0, dt, substeps, seed, v, q, w, c, h);
   PContract pa;
   pa.l[0] = lam[0]; pa.l[1] = lam[1]; pa.l[2] = lam[2];
   pa.tot = jconst((lam[0] * x0.p[0] + lam[1] * x0.p[1]) + lam[2] * x0.p[2]);
-  state_update_jet<MODEL>(P, v, q, w, c, h, substeps, normalise, pa);
+  state_update_jet<MODEL, PContract, NET>(P, v, q, w, c, h, substeps, normalise, pa, net);
   Jet L = pa.tot;
 #pragma unroll
   for (int i = 0; i < 3; ++i) { L = jfma(lam[3 + i], v[i], L); L = jfma(lam[10 + i], w[i], L); }
@@ -179,12 +306,13 @@ struct HessArgs {
   float* value;              // optional [n]: lambda^T Phi
 };
 
-template <bool SOA, int MODEL = 0>
+// SHARED (network model, short horizons): one node per 64-thread block, the network through NetSharedJet.
+template <bool SOA, int MODEL = 0, bool SHARED = false>
 __global__ void __launch_bounds__(128)
 hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
   const long long gt = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long node = gt / HESS_LANES;
-  if (node >= a.n) return;
+  if (node >= a.n) return;   // SHARED: blockDim.x == HESS_LANES, so a block leaves as a whole
   const int t = (int)(gt % HESS_LANES);
   HessSeed seed;
   hess_task(t, seed.i, seed.j0, seed.j1);
@@ -195,7 +323,17 @@ hessian_kernel(const __grid_constant__ DevConst P, const HessArgs a) {
 #pragma unroll
   for (int r = 0; r < 13; ++r) lam[r] = __ldg(a.lam.base + node * a.lam.sb + r * a.lam.sc);
   const float dt = a.dt_per_node ? __ldg(a.dt_per_node + node) : a.dt;
-  const Jet L = lagrangian_step_jet<MODEL>(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed);
+  Jet L;
+  if constexpr (SHARED) {
+    __shared__ float prod[32 * NJS_ROW];
+    __shared__ float sums[NJS_SUMS];
+    NetSharedJet net;
+    net.prod = prod; net.sums = sums; net.t = t;
+    net_unit_weights(P, t & 31, net.w);
+    L = lagrangian_step_jet<MODEL, NetSharedJet>(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed, net);
+  } else {
+    L = lagrangian_step_jet<MODEL>(P, s, c, dt, a.substeps, a.normalise != 0, lam, seed);
+  }
   const long long es = SOA ? a.n : 1;
   float* Hn = a.H + (SOA ? node : node * (NZ * NZ));
   const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);

@@ -182,9 +182,34 @@ AIRC_HD void alt_coefficients_jet(const DevConst& P, const Jet vb[3], const Jet&
 // to the caller.  MODEL 0: the NN surrogate; 1: the table models of airc_alt.cuh.
 // J is the jet type: Jet (second order) or Dual (value + two first-order directions, airc_hess2.cuh); the
 // table models exist on Jet only.
-template <int MODEL = 0, class J = Jet>
+// NET evaluates the network model's coefficients: NetInlineJet = every thread the whole network on its jets;
+// NetSharedJet (airc_hess.cuh) = the 64 threads of a node share the value-level sums.
+struct NetInlineJet {
+  template <class J>
+  AIRC_HD void operator()(const DevConst& P, const J& da, const J& de, const J& qbar, const J& alpha, const J& beta,
+                          J C[6]) const {
+#pragma unroll
+    for (int k = 0; k < 6; ++k) C[k] = J::cst(P.net.c0[k]);
+#pragma unroll 2
+    for (int j = 0; j < NH; ++j) {
+      const HidPair& hp = P.net.hid[j >> 1];
+      const int e = j & 1;
+      J h = J::cst(hp.a0[e]);
+      h = jfma(hp.Au[0][e], da, h);
+      h = jfma(hp.Au[1][e], de, h);
+      h = jfma(hp.Ax[0][e], qbar, h);
+      h = jfma(hp.Ax[1][e], alpha, h);
+      h = jfma(hp.Ax[2][e], beta, h);
+      const J r = jsigm2(h);
+#pragma unroll
+      for (int k = 0; k < 6; ++k) C[k] = jfma(P.net.Wo[k][j], r, C[k]);
+    }
+  }
+};
+
+template <int MODEL = 0, class J = Jet, class NET = NetInlineJet>
 AIRC_HD void f_jet(const DevConst& P, const J v[3], const J q[4], const J w[3], const CtlT<J>& c,
-                   J vdot[3], J qdot[4], J wdot[3]) {
+                   J vdot[3], J qdot[4], J wdot[3], const NET& net = NET()) {
   const J &x = q[0], &y = q[1], &z = q[2], &s = q[3];
   const J xx = x * x, yy = y * y, zz = z * z, ww = s * s;
   const J n2 = (xx + yy) + (zz + ww);
@@ -214,22 +239,7 @@ AIRC_HD void f_jet(const DevConst& P, const J v[3], const J q[4], const J w[3], 
 
   J C[6];
   if constexpr (MODEL == 0) {
-#pragma unroll
-    for (int k = 0; k < 6; ++k) C[k] = J::cst(P.net.c0[k]);
-#pragma unroll 2
-    for (int j = 0; j < NH; ++j) {
-      const HidPair& hp = P.net.hid[j >> 1];
-      const int e = j & 1;
-      J h = J::cst(hp.a0[e]);
-      h = jfma(hp.Au[0][e], c.da, h);
-      h = jfma(hp.Au[1][e], c.de, h);
-      h = jfma(hp.Ax[0][e], qbar, h);
-      h = jfma(hp.Ax[1][e], alpha, h);
-      h = jfma(hp.Ax[2][e], beta, h);
-      const J r = jsigm2(h);
-#pragma unroll
-      for (int k = 0; k < 6; ++k) C[k] = jfma(P.net.Wo[k][j], r, C[k]);
-    }
+    net(P, c.da, c.de, qbar, alpha, beta, C);
   } else {
     alt_coefficients_jet(P, vb, qbar, alpha, beta, w, c, C);
   }

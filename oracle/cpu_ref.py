@@ -237,6 +237,17 @@ class HostEmul:
                               1 if normalise else 0, H, g, v)
         return H, g, v
 
+    def hessian_shared(self, x, u, lam, dt, substeps=1, normalise=False):
+        """K4 arithmetic for short horizons (jets, the network's sums shared by the 64 threads of a node)."""
+        x, u, lam = (np.ascontiguousarray(a, np.float32) for a in (x, u, lam))
+        n = x.shape[0]
+        H, g, v = np.empty((n, 21, 21), np.float32), np.empty((n, 21), np.float32), np.empty(n, np.float32)
+        self.lib.emul_hessian_shared.argtypes = [_PP, _NP, _f32, _f32, _f32, C.c_float, C.c_int64, C.c_int,
+                                                 C.c_uint32, _f32, _f32, _f32]
+        self.lib.emul_hessian_shared(C.byref(self.params), C.byref(self.blob), x, u, lam, float(dt), n, substeps,
+                                     1 if normalise else 0, H, g, v)
+        return H, g, v
+
     def hessian2(self, x, u, lam, dt, substeps=1, normalise=False):
         """K4 arithmetic (airc_hess2.cuh, forward over reverse) on the host: H[n,21,21], grad[n,21], value[n]."""
         x, u, lam = (np.ascontiguousarray(a, np.float32) for a in (x, u, lam))

@@ -305,6 +305,39 @@ void emul_hessian(const AircParams* p, const AircNNBlob* nn, const float* x, con
   }
 }
 
+// K4 arithmetic for short horizons (airc_hess.cuh, NetSharedJet): the jets with the network's value-level sums
+// shared by the 64 threads of a node; every task adds the 32 units' terms in the device's order.
+void emul_hessian_shared(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,
+                         float dt, int64_t n, int substeps, uint32_t flags, float* H, float* grad, float* value) {
+  DevConst P;
+  build_devconst(*p, *nn, P);
+  memset(H, 0, sizeof(float) * NZ * NZ * n);
+  NetSharedJet net;
+  net.prod = net.sums = nullptr;
+  for (int64_t i = 0; i < n; ++i) {
+    State s; Ctl c;
+    load(x + 13 * i, u + 7 * i, s, c);
+    float* Hn = H + i * NZ * NZ;
+    float* g = grad + i * NZ;
+    for (int r = 0; r < 3; ++r) { g[r] = lam[13 * i + r]; g[16 + r] = 0.f; }
+    for (int t = 0; t < HESS_LANES; ++t) {
+      HessSeed seed;
+      hess_task(t, seed.i, seed.j0, seed.j1);
+      net.t = t;
+      const Jet L = lagrangian_step_jet<0, NetSharedJet>(P, s, c, dt, substeps, flags & AIRC_FLAG_NORMALISE,
+                                                         lam + 13 * i, seed, net);
+      const int zi = hess_zindex(seed.i), z0 = hess_zindex(seed.j0);
+      Hn[zi * NZ + z0] = Hn[z0 * NZ + zi] = L.og.lo;
+      if (seed.j1 < NHACT) {
+        const int z1 = hess_zindex(seed.j1);
+        Hn[zi * NZ + z1] = Hn[z1 * NZ + zi] = L.og.hi;
+      }
+      if (seed.j0 == seed.i) g[zi] = L.o;
+      if (t == 0) value[i] = L.v;
+    }
+  }
+}
+
 // K4 arithmetic (airc_hess2.cuh, forward over reverse): the eight lanes of a node, one after the other, and the
 // kernel's write-out (entries i <= j of column j with their mirror image).
 void emul_hessian2(const AircParams* p, const AircNNBlob* nn, const float* x, const float* u, const float* lam,

@@ -1,6 +1,6 @@
 """K4 (airc_hessian, network model) per C-ABI call on prepared device buffers over node counts, AoS and SoA,
 CUDA events around every call, L2 flushed between calls.  Usage: python profiles/time_hessian_sizes.py [variant.so]
-(sizes: HESS_SIZES=298,4096,...)."""
+(sizes: HESS_SIZES=298,4096,...; HESS_NOFLUSH=1 keeps L2 warm between calls)."""
 import os
 import sys
 from pathlib import Path
@@ -20,7 +20,7 @@ tag = Path(sys.argv[1]).stem if len(sys.argv) > 1 else "shipped"
 ac = Aircraft.from_problem(com=TRIM_COM, device=0, physical_integration_substeps=1, normalise=True)
 lib, h = ac._lib, ac.handle
 st = torch.cuda.current_stream().cuda_stream
-flush = torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
+flush = None if os.environ.get("HESS_NOFLUSH") else torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
 sizes = [int(s) for s in os.environ.get("HESS_SIZES", "64,149,298,600,1200,2400,4800,9600,65536,262144").split(",")]
 for n in sizes:
     x = torch.tensor(make_states(n, seed=5, perturb_norm=1e-3), dtype=torch.float32, device=dev)

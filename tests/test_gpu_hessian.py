@@ -46,7 +46,7 @@ def test_hessian_parity(ac, orc, substeps, normalise, dt):
     assert np.abs(v.cpu().numpy() - vo).max() < PARITY_TOL * np.abs(vo).max()
 
 
-@pytest.mark.parametrize("n", [300, 1500])            # the jets kernel / the forward-over-reverse kernel
+@pytest.mark.parametrize("n", [300, 1500])            # the shared-network jets kernel / the forward-over-reverse kernel
 def test_hessian_structure_layouts_and_host_path(ac, n):
     x, u, lam = _inputs(n, 52)
     H, g, _ = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.01)
@@ -72,8 +72,9 @@ def test_hessian_structure_layouts_and_host_path(ac, n):
 def test_hessian_two_formulations_agree(ac, orc):
     """airc_hessian runs the network model's long batches by forward over reverse (airc_hess2.cuh, eight lanes per
     node sharing the network through shuffles) and short horizons (up to three nodes per SM) on second-order
-    jets (airc_hess.cuh): the same nodes through both, against each other and against the oracle, and the last
-    partial warp of the long batch (idle lanes keep step for the shuffles)."""
+    jets (airc_hess.cuh; one node per 64-thread block, the network's sums shared through shared memory): the same
+    nodes through both, against each other and against the oracle, and the last partial warp of the long batch
+    (idle lanes keep step for the shuffles).  More than 8 substeps on a long batch: the unshared jets kernel."""
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     n_short, n_long = 3 * sms, 3 * sms + 5           # 5 nodes = 40 lanes: one full warp and a quarter of the next
     x, u, lam = _inputs(n_long, 54)

@@ -92,13 +92,15 @@ def test_linearize_packed_dt_column(pair, substeps, normalise):
     assert np.allclose(D0.numpy(), orc.state_derivative(t64(x), t64(u)).numpy(), rtol=1e-6, atol=1e-6)
 
 
-@pytest.mark.parametrize("arith", ["hessian2", "hessian"])
+@pytest.mark.parametrize("arith", ["hessian2", "hessian_shared", "hessian"])
 @pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (2, True), (3, False)])
 def test_lagrangian_hessian_jets(pair, substeps, normalise, arith):
     """K4 arithmetic against jacfwd(jacfwd(lam^T Phi)) of the float64 oracle over z = (x, u, dt), both forms:
     `hessian2` = forward over reverse (airc_hess2.cuh: the hand-written adjoint sweep of the RK4 step on dual
     numbers, eight lanes per node; what airc_hessian runs for the network model), `hessian` = second-order
-    forward mode (airc_jet.cuh / airc_hess.cuh: 64 (outer, inner-pair) tasks per node; the table models)."""
+    forward mode (airc_jet.cuh / airc_hess.cuh: 64 (outer, inner-pair) tasks per node; the table models),
+    `hessian_shared` = the same jets with the network's value-level sums (C, dC/dy, d2C/dy2) shared by the 64
+    threads of a node (NetSharedJet; what short horizons of the network model run)."""
     emu, orc = pair
     n = 96
     x, u = make_states(n, seed=27, perturb_norm=1e-3), make_controls(n, seed=27)
@@ -125,7 +127,7 @@ def test_lagrangian_hessian_jets_stall_scaling(built):
     x[:32, 3:6] *= np.array([0.6, 1.0, 2.0])             # large alpha: the scaling is active
     lam = np.random.default_rng(28).normal(size=(n, 13)).astype(np.float32)
     Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.01))
-    for arith in (emu.hessian2, emu.hessian):
+    for arith in (emu.hessian2, emu.hessian_shared, emu.hessian):
         H, g, v = arith(x, u, lam, 0.01)
         assert col_err(H, Ho, atol=1e-3) < PARITY_TOL and col_err(g, go) < PARITY_TOL
         assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
