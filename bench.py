@@ -852,9 +852,10 @@ def side_extras(torch, ac, dev, args):
                 "executed_flops_per_eval": ex, "dram_bytes_per_eval": by,
                 "algorithmic_bytes_per_eval": 4 * (13 + 7 + 13 + 441 + 21),
                 "issue_active_pct_under_ncu": aud.get("issue_active_pct"),
-                "note": "instruction-fetch bound rather than FMA bound: ~17 k straight-line instructions per thread with "
-                        "two warps per scheduler (profiles/r2_variants_hessian.txt); the value parts are the same in the "
-                        "eight lanes of a node, so about a third of the executed flops are replicated work",
+                "note": "latency bound rather than FMA bound: ~17 k straight-line instructions per thread with two warps "
+                        "per scheduler at 255 registers, waiting on its own spills (profiles/r2_variants_hessian.txt); the "
+                        "value parts are the same in the eight lanes of a node, so about a third of the executed flops "
+                        "are replicated work",
                 "source": f"profiles/{aud['capture']} via profiles/r2_kernel_audit.json (EXECUTED flops); CUDA sources "
                           f"{'CHANGED since' if aud['stale'] else 'unchanged since'} the capture"}
     return out

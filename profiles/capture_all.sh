@@ -6,3 +6,6 @@ python bench.py > gpurun_out/r3h_bench_n1.json 2> gpurun_out/bench.err
 tail -c 600 gpurun_out/r3h_bench_n1.json
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r3h_launches.csv python bench.py --steps 2 --warmup 1 > gpurun_out/ncu_bench.log 2>&1
 ls -la gpurun_out | tail -12
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
+python -m pytest tests/test_zz_no_alloc.py -x -q 2>&1 | tail -2
+python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -3
