@@ -92,9 +92,8 @@ def test_linearize_packed_dt_column(pair, substeps, normalise):
     assert np.allclose(D0.numpy(), orc.state_derivative(t64(x), t64(u)).numpy(), rtol=1e-6, atol=1e-6)
 
 
-@pytest.mark.parametrize("arith", ["hessian2", "hessian_shared", "hessian"])
 @pytest.mark.parametrize("substeps,normalise", [(1, False), (1, True), (2, True), (3, False)])
-def test_lagrangian_hessian_jets(pair, substeps, normalise, arith):
+def test_lagrangian_hessian_jets(pair, substeps, normalise):
     """K4 arithmetic against jacfwd(jacfwd(lam^T Phi)) of the float64 oracle over z = (x, u, dt), both forms:
     `hessian2` = forward over reverse (airc_hess2.cuh: the hand-written adjoint sweep of the RK4 step on dual
     numbers, eight lanes per node; what airc_hessian runs for the network model), `hessian` = second-order
@@ -102,17 +101,19 @@ def test_lagrangian_hessian_jets(pair, substeps, normalise, arith):
     `hessian_shared` = the same jets with the network's value-level sums (C, dC/dy, d2C/dy2) shared by the 64
     threads of a node (NetSharedJet; what short horizons of the network model run)."""
     emu, orc = pair
-    n = 96
+    n = 40
     x, u = make_states(n, seed=27, perturb_norm=1e-3), make_controls(n, seed=27)
     lam = np.random.default_rng(27).normal(size=(n, 13)).astype(np.float32)
-    H, g, v = getattr(emu, arith)(x, u, lam, 0.02, substeps, normalise)
     Ho, go, vo = (a.numpy() for a in orc.lagrangian_hessian(t64(x), t64(u), t64(lam), 0.02, substeps, normalise))
-    assert col_err(H, Ho, atol=1e-3) < PARITY_TOL        # every entry against its own scale over the batch
-    assert col_err(g, go) < PARITY_TOL
-    assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max()
-    assert np.array_equal(H, H.transpose(0, 2, 1))
     inert = [0, 1, 2, 16, 17, 18]                        # p never enters f; thrust is inert (aircraft.py:320)
-    assert not H[:, inert, :].any() and not Ho[:, inert, :].any()
+    assert not Ho[:, inert, :].any()
+    for arith in ("hessian2", "hessian_shared", "hessian"):
+        H, g, v = getattr(emu, arith)(x, u, lam, 0.02, substeps, normalise)
+        assert col_err(H, Ho, atol=1e-3) < PARITY_TOL, arith   # every entry against its own scale over the batch
+        assert col_err(g, go) < PARITY_TOL, arith
+        assert np.abs(v - vo).max() < PARITY_TOL * np.abs(vo).max(), arith
+        assert np.array_equal(H, H.transpose(0, 2, 1)), arith
+        assert not H[:, inert, :].any(), arith
     # the gradient is [A B dPhi/ddt]^T lam
     xo, A, B, Dt = orc.linearize(t64(x), t64(u), 0.02, substeps, normalise, want_dt=True)
     J = np.concatenate([A.numpy(), B.numpy(), Dt.numpy()[:, :, None]], axis=2)
