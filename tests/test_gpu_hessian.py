@@ -97,6 +97,20 @@ def test_hessian_two_formulations_agree(ac, orc):
     assert col_err(H8.cpu(), Ho8) < PARITY_TOL and col_err(g8.cpu(), go8) < PARITY_TOL
 
 
+def test_hessian_block_size_switch(ac):
+    """Long batches run 256-thread blocks (from 256 nodes per SM), shorter ones 128: the same nodes give the same
+    bits either way (a node's eight lanes never see the block), including the mostly idle last block."""
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    n_long = 256 * sms + 1                            # 256-thread blocks, one live node in the last block
+    x, u, lam = _inputs(n_long, 55)
+    Hl, gl, vl = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.01, normalise=True, want_value=True)
+    for lo, hi in ((0, 700), (n_long - 700, n_long)):  # the same nodes in a batch of 700: 128-thread blocks
+        Hs, gs, vs = ac.lagrangian_hessian(f32(x[lo:hi]), f32(u[lo:hi]), f32(lam[lo:hi]), 0.01, normalise=True,
+                                           want_value=True)
+        assert torch.equal(Hl[lo:hi], Hs) and torch.equal(gl[lo:hi], gs) and torch.equal(vl[lo:hi], vs)
+    assert torch.isfinite(Hl).all() and torch.equal(Hl, Hl.transpose(1, 2))
+
+
 def test_hessian_gradient_matches_jacobian_kernel(ac):
     """grad = [A B dPhi/ddt]^T lam: K3's first-order part against K2 (separately written tangents)."""
     n = 2048
