@@ -1,4 +1,4 @@
-// airc_hess.cuh -- K3: Hessian of the multiplier-weighted step, H = d2 (lambda^T Phi) / dz2 with
+// airc_hess.cuh -- K4 (second-order jets): Hessian of the multiplier-weighted step, H = d2 (lambda^T Phi) / dz2 with
 // z = (x[13], u[7], dt), and its gradient, at n shooting nodes.
 //
 // Replaces CasADi's second-order AD behind IPOPT's exact nlp_hess_l

@@ -5,14 +5,16 @@
 // belong to time='progress', control/base.py:276,306-307), like airc_hess.cuh, with a tenth of its arithmetic:
 //
 //   L(z) = lambda^T Phi(x, u, dt),  z = (x, u, dt);  g(z) = dL/dz by ONE hand-written reverse sweep through the
-//   RK4 step (f_vjp below is the adjoint of f); H = dg/dz by running that sweep on DUAL numbers: every quantity
-//   carries its value and its derivatives along TWO input directions, packed into the lanes of FFMA2.
-//   15 directions are active (v q w | aileron elevator rudder flaps | dt), so EIGHT threads per node give the
-//   whole 15 x 15 block (airc_hess.cuh needs 64 threads per node, each on second-order jets).
+//   RK4 step (f_dual<true> below is f with its adjoint); H = dg/dz by running that sweep on DUAL numbers: every
+//   quantity carries its value and its derivatives along TWO input directions, packed into the lanes of FFMA2.
+//   15 directions are active (v q w | aileron elevator rudder flaps | dt), so EIGHT threads ("lanes") per node give
+//   the whole 15 x 15 block (airc_hess.cuh needs 64 threads per node, each on second-order jets).  The network's
+//   value-level sums are the same in the eight lanes, which share them through shuffles (net_linearise).
 //
 // The sweep keeps no tape: the forward pass stores the three stage derivatives k1..k3 of a substep, the reverse
-// pass rebuilds each stage point from them and f_vjp recomputes f's interior.  Only the NN surrogate
-// (model 0) has a hand-written adjoint; the table models stay on airc_hess.cuh.
+// pass rebuilds each stage point from them and f_dual<true> recomputes f's interior.  Only the NN surrogate
+// (model 0) has a hand-written adjoint; the table models stay on airc_hess.cuh, and so do short horizons (there
+// the 64 threads of a node share the network, NetSharedJet).  Measured variants: profiles/r2_variants_hessian.txt.
 #pragma once
 #include <type_traits>
 #include "airc_hess.cuh"
@@ -536,8 +538,8 @@ AIRC_HD void rk4_reverse_dual(const DevConst& P, const float* tab, int sub, cons
   xb = xacc;
 }
 
-// One of the eight lanes of a node.  g[i].v = dL/dz_i and g[i].t = (H[i][j0], H[i][j1]) over the 15 active
-// directions i, j0 = 2 lane, j1 = 2 lane + 1 (j1 = 15 on the last lane: unused); value = lambda^T Phi.
+// One of the eight lanes of a node.  g[i].v = dL/dz_i and g[i].t = (H[i][j0], H[i][j0 + 1]) over the 15 active
+// directions i, j0 = 2 lane (direction 15 on the last lane: unused); value = lambda^T Phi.
 // tab: the weight image of net_tab_entry.  On the device the eight lanes of a node run in lockstep (the network
 // sums cross them); the host runs them one after the other.
 AIRC_HD void hessian2_lane(const DevConst& P, const float* tab, const State& x0, const Ctl& c0, float dt, int substeps,

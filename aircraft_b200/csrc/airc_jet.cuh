@@ -1,4 +1,4 @@
-// airc_jet.cuh -- second-order forward-mode arithmetic for the Lagrangian Hessian kernel (K3).
+// airc_jet.cuh -- second-order forward-mode arithmetic for the Lagrangian Hessian kernel (K4, jets formulation).
 //
 // What it replaces: IPOPT's nlp_hess_l with hessian_approximation 'exact'
 // (/root/reference/src/aircraft/config.py:29), i.e. CasADi's second-order AD of the defect
