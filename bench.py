@@ -676,7 +676,7 @@ def measure_jacobian(torch, ac, dev, rank, world, K, fp32_peak_tflops, rank_max,
     windows.append((t_mark, clocks.mark()))
     gbs = n * B_JAC / (ms * 1e-3) / 1e9
     ex = audit["executed_fp32_flops_per_unit"] if audit else None
-    roof = {"kernel": "linearize_tile_kernel<128,soa>", "bound": "fp32 (reported in GB/s as north_star asks; intensity "
+    roof = {"kernel": "linearize_tile_kernel<64,soa> (64-node tiles, two blocks per SM)", "bound": "fp32 (reported in GB/s as north_star asks; intensity "
             "~25 flop/B is above the machine balance ~11)", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
             "frac": gbs / peaks["hbm_gbs"], "peak_source": peak_src, "bytes_per_eval": B_JAC,
             "traffic": audit["dram_bytes_per_unit"] * n if audit else None,
