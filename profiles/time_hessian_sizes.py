@@ -1,6 +1,6 @@
 """K4 (airc_hessian, network model) per C-ABI call on prepared device buffers over node counts, AoS and SoA,
 CUDA events around every call, L2 flushed between calls.  Usage: python profiles/time_hessian_sizes.py [variant.so]
-(sizes: HESS_SIZES=298,4096,...; HESS_NOFLUSH=1 keeps L2 warm between calls)."""
+(sizes: HESS_SIZES=298,4096,...; HESS_NOFLUSH=1 keeps L2 warm between calls; HESS_MODEL=poly|linear|default: a table model)."""
 import os
 import sys
 from pathlib import Path
@@ -17,7 +17,8 @@ from bench import time_launches
 dev = torch.device("cuda", 0)
 torch.manual_seed(0)
 tag = Path(sys.argv[1]).stem if len(sys.argv) > 1 else "shipped"
-ac = Aircraft.from_problem(com=TRIM_COM, device=0, physical_integration_substeps=1, normalise=True)
+ac = Aircraft.from_problem(com=TRIM_COM, device=0, physical_integration_substeps=1, normalise=True,
+                           coeff_model_type=os.environ.get("HESS_MODEL", "nn"))
 lib, h = ac._lib, ac.handle
 st = torch.cuda.current_stream().cuda_stream
 flush = None if os.environ.get("HESS_NOFLUSH") else torch.zeros(64 * 1024 * 1024, dtype=torch.float32, device=dev)
