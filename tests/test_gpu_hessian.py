@@ -111,6 +111,30 @@ def test_hessian_block_size_switch(ac):
     assert torch.isfinite(Hl).all() and torch.equal(Hl, Hl.transpose(1, 2))
 
 
+@pytest.mark.parametrize("n", [200, 1500, 40000])     # shared-network jets / forward over reverse, 128 / 256 threads
+@pytest.mark.parametrize("layout", ["aos", "soa"])
+def test_hessian_overwrites_every_entry(ac, n, layout):
+    """airc_hessian leaves no entry of H, grad, value as it found it (the structural zeros come from a memset on the
+    jets paths and from the kernel itself on the forward-over-reverse path): outputs pre-filled with NaN."""
+    from aircraft_b200 import _cabi
+    x, u, lam = _inputs(n, 56)
+    soa = layout == "soa"
+    xd, ud, ld = (f32(a.T.copy() if soa else a) for a in (x, u, lam))
+    H = torch.full((n * 441,), float("nan"), device=DEV)
+    g = torch.full((n * 21,), float("nan"), device=DEV)
+    v = torch.full((n,), float("nan"), device=DEV)
+    rc = ac._lib.airc_hessian(ac.handle, xd.data_ptr(), ud.data_ptr(), ld.data_ptr(), 0.01, None, n, 1, 1,
+                              _cabi.LAYOUT_SOA if soa else _cabi.LAYOUT_AOS, H.data_ptr(), g.data_ptr(), v.data_ptr(),
+                              torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    assert torch.isfinite(H).all() and torch.isfinite(g).all() and torch.isfinite(v).all()
+    Hn = H.view(21, 21, n).permute(2, 0, 1) if soa else H.view(n, 21, 21)
+    inert = [0, 1, 2, 16, 17, 18]
+    assert torch.count_nonzero(Hn[:, inert, :]) == 0 and torch.count_nonzero(Hn[:, :, inert]) == 0
+    Hf, gf, vf = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.01, normalise=True, want_value=True)
+    assert torch.equal(Hn, Hf) and torch.equal(v, vf)
+
+
 def test_hessian_gradient_matches_jacobian_kernel(ac):
     """grad = [A B dPhi/ddt]^T lam: K3's first-order part against K2 (separately written tangents)."""
     n = 2048
