@@ -454,8 +454,12 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
     barrier()
     windows.append((t_mark, clocks.mark()))
     ms_total = s0.elapsed_time(s1)
+    ms_by_rank = [ms_total / K]
     if world > 1:
         t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        every = torch.empty(world, dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(every, t)
+        ms_by_rank = [float(v) / K for v in every.tolist()]     # every rank's own device time: the spread between GPUs
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms_total = float(t.item())
     # kernel duration: the same sweep launched eagerly, CUDA events around airc_sweep (stream = torch's current)
@@ -470,6 +474,11 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
     value = total * H / (ms_step * 1e-3)
     launches = K * (3 + (1 if world > 1 else 0))      # prep, sweep2, winner2 (+ select_record)
     ms_roll = sum(a.elapsed_time(b) for a, b in roll_events) / K
+    kernel_ms_by_rank = [ms_roll]
+    if world > 1:   # every GPU's own kernel time (no exchange inside): the step waits for the slowest one
+        every = torch.empty(world, dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(every, torch.tensor([ms_roll], dtype=torch.float64, device=dev))
+        kernel_ms_by_rank = [float(v) for v in every.tolist()]
     roll_tflops = per_gpu * H * F_STEP / (ms_roll * 1e-3) / 1e12
     peak = fp32_peak(ac)
 
@@ -569,6 +578,7 @@ def run_c4(torch, dist, ac, dev, rank, world, per_gpu, total, K, W, clocks, wind
         "metric": "surrogate RK4 state-steps/s", "value": value, "unit": "state-steps/s",
         "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "ms_per_step_by_rank": ms_by_rank, "kernel_ms_by_rank": kernel_ms_by_rank,
         "config": workload_config("c4", per_gpu, world),
         "sustained": sustained, "config4_strong": strong,
         "e2e": {"value": e2e_value, "unit": "state-steps/s", "h2d_bytes_per_step": h2d,
