@@ -394,11 +394,11 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
 #define AIRC_AB_HESS_JETS 0
 #endif
 #ifndef AIRC_AB_HESS_SMALL         // build-variant A/B only: node count per SM up to which the jets kernel runs
-#define AIRC_AB_HESS_SMALL 3
+#define AIRC_AB_HESS_SMALL 4
 #endif
   if (!h->dc.model && substeps <= HESS2_MAXSUB && !AIRC_AB_HESS_JETS && n > (long long)AIRC_AB_HESS_SMALL * h->sm_count) {
     // the NN surrogate: forward over reverse, eight threads per node (airc_hess2.cuh).  Short horizons (up to
-    // three nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
+    // four nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
     const int bs2 = AIRC_AB_H2_BS ? AIRC_AB_H2_BS : (n * HESS2_LANES >= (long long)h->sm_count * 256 * 8 ? 256 : 128);
     const unsigned grid = (unsigned)((n * HESS2_LANES + bs2 - 1) / bs2);
 #define AIRC_H2_LAUNCH(BS_)                                                                   \

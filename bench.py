@@ -846,7 +846,7 @@ def side_extras(torch, ac, dev, args):
         ms = time_launches(torch, lambda: ac.lagrangian_hessian(x, u, lam, DT, layout="soa", normalise=True), K, 3, flush)
         out[name] = {"workload": f"d2(lambda^T Phi)/d(x,u,dt)^2 [21x21] + gradient at {nh} shooting nodes (SoA)",
                      "kernel": "second-order jets, 64 threads per node (short horizon)"
-                               if nh <= 3 * torch.cuda.get_device_properties(dev).multi_processor_count
+                               if nh <= 4 * torch.cuda.get_device_properties(dev).multi_processor_count
                                else "forward over reverse, 8 lanes per node",
                      "value": nh / (ms * 1e-3), "unit": "hessian-evals/s", "ms_per_launch": ms,
                      "l2": "flushed between launches",

@@ -214,7 +214,7 @@ int airc_defects(const AircHandle* h, const float* x, const float* u, const floa
  * dt row/column serves time='progress', control/base.py:276,306-307).  15 directions are active; rows
  * and columns of p and thrust are exactly zero; H is symmetric to the bit.  The network model runs
  * forward over reverse (a hand-written adjoint sweep of the RK4 step on dual numbers, 8 threads per
- * node); short horizons (up to 3 nodes per SM; there the 64 threads share the network's sums), the
+ * node); short horizons (up to 4 nodes per SM; there the 64 threads share the network's sums), the
  * table models and more than 8 substeps run second-order forward mode on 64 threads per node.  The
  * formulations agree to 7e-7 of an entry's scale, so a node's block depends on the batch it is
  * evaluated in only at that level.

@@ -33,9 +33,9 @@ def _inputs(n, seed):
     return x, u, lam
 
 
+@pytest.mark.parametrize("n", [300, 700])             # the shared-network jets kernel / the forward-over-reverse kernel
 @pytest.mark.parametrize("substeps,normalise,dt", [(1, False, 0.01), (1, True, 0.02), (3, True, 0.03)])
-def test_hessian_parity(ac, orc, substeps, normalise, dt):
-    n = 515
+def test_hessian_parity(ac, orc, substeps, normalise, dt, n):
     x, u, lam = _inputs(n, 51)
     H, g, v = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), dt, substeps=substeps, normalise=normalise,
                                     want_value=True)
@@ -71,12 +71,12 @@ def test_hessian_structure_layouts_and_host_path(ac, n):
 
 def test_hessian_two_formulations_agree(ac, orc):
     """airc_hessian runs the network model's long batches by forward over reverse (airc_hess2.cuh, eight lanes per
-    node sharing the network through shuffles) and short horizons (up to three nodes per SM) on second-order
+    node sharing the network through shuffles) and short horizons (up to four nodes per SM) on second-order
     jets (airc_hess.cuh; one node per 64-thread block, the network's sums shared through shared memory): the same
     nodes through both, against each other and against the oracle, and the last partial warp of the long batch
     (idle lanes keep step for the shuffles).  More than 8 substeps on a long batch: the unshared jets kernel."""
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    n_short, n_long = 3 * sms, 3 * sms + 5           # 5 nodes = 40 lanes: one full warp and a quarter of the next
+    n_short, n_long = 4 * sms, 4 * sms + 5           # 5 nodes = 40 lanes: one full warp and a quarter of the next
     x, u, lam = _inputs(n_long, 54)
     Hl, gl, vl = ac.lagrangian_hessian(f32(x), f32(u), f32(lam), 0.02, normalise=True, want_value=True)
     Hs, gs, vs = ac.lagrangian_hessian(f32(x[:n_short]), f32(u[:n_short]), f32(lam[:n_short]), 0.02, normalise=True,
