@@ -399,7 +399,12 @@ int airc_hessian(const AircHandle* h, const float* x, const float* u, const floa
   if (!h->dc.model && substeps <= HESS2_MAXSUB && !AIRC_AB_HESS_JETS && n > (long long)AIRC_AB_HESS_SMALL * h->sm_count) {
     // the NN surrogate: forward over reverse, eight threads per node (airc_hess2.cuh).  Short horizons (up to
     // four nodes per SM) stay on the jets: 64 threads per node finish one node sooner than eight do.
-    const int bs2 = AIRC_AB_H2_BS ? AIRC_AB_H2_BS : (n * HESS2_LANES >= (long long)h->sm_count * 256 * 8 ? 256 : 128);
+    // One wave = 32 nodes per SM either way.  A wave of one 256-thread block per SM takes 0.88 of the time of a wave
+    // of two 128-thread blocks (the warps share the fetch of the straight-line code), but a straggling 256-thread
+    // block costs a whole wave time where 128-thread blocks refill half an SM at a time: the larger block when its
+    // whole waves are cheaper than the smaller block's fractional ones (profiles/r2_variants_hessian.txt).
+    const double waves = (double)n / (32.0 * h->sm_count);
+    const int bs2 = AIRC_AB_H2_BS ? AIRC_AB_H2_BS : (ceil(waves) * 0.88 <= waves + 0.1 ? 256 : 128);
     const unsigned grid = (unsigned)((n * HESS2_LANES + bs2 - 1) / bs2);
 #define AIRC_H2_LAUNCH(BS_)                                                                   \
     do {                                                                                      \
