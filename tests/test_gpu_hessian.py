@@ -98,7 +98,7 @@ def test_hessian_two_formulations_agree(ac, orc):
 
 
 def test_hessian_block_size_switch(ac):
-    """Long batches run 256-thread blocks (from 256 nodes per SM), shorter ones 128: the same nodes give the same
+    """Long batches run 256-thread blocks (always from 6.5 waves of 32 nodes per SM on), short ones 128: the same nodes give the same
     bits either way (a node's eight lanes never see the block), including the mostly idle last block."""
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     n_long = 256 * sms + 1                            # 256-thread blocks, one live node in the last block
